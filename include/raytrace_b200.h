@@ -1,0 +1,177 @@
+/* raytrace_b200.h — C ABI of the B200-native batched whistler ray tracer.
+ *
+ * Drop-in boundary for the hot path of andersontodds/ray-trace.  The reference has
+ * no FFI of its own: its boundary is the set of Julia functions and the SciML solve convention
+ * cited beside each entry point below (file:line into the reference tree).  A Julia host binds
+ * these symbols with `ccall` (see INTEGRATION.md and julia/RayTraceB200.jl); the Python mirror in
+ * ray-trace_b200/api.py binds the same symbols with ctypes.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every array the caller receives back is caller-allocated;
+ *   - all functions return 0 on success, a negative rt_error otherwise; rt_last_error() gives text;
+ *   - per-ray numerical failures are DATA (status[]), never API errors;
+ *   - a context owns one CUDA device, one stream and its device buffers; it is not thread-safe;
+ *   - there is NO CPU fallback: without a usable CUDA device rt_create fails with RT_ERR_NO_DEVICE.
+ */
+#ifndef RAYTRACE_B200_H
+#define RAYTRACE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_API __attribute__((visibility("default")))
+
+typedef enum rt_error {
+  RT_OK = 0,
+  RT_ERR_INVALID = -1,   /* bad argument */
+  RT_ERR_NO_DEVICE = -2, /* no CUDA device / driver */
+  RT_ERR_CUDA = -3,      /* CUDA runtime error (text in rt_last_error) */
+  RT_ERR_NOMEM = -4,
+  RT_ERR_STATE = -5      /* call order (e.g. trajectory copy before a solve) */
+} rt_error;
+
+/* Variant presets: which reference file's constants, geometry and signs are used. */
+typedef enum rt_preset {
+  RT_PRESET_LAT2D = 0,   /* RayTrace_lat.jl: theta slot = latitude, CA92 plasmasphere            */
+  RT_PRESET_RAY3D = 1,   /* RayTrace_3D.jl: colatitude, refractive-index vector rho, group delay */
+  RT_PRESET_RAYMAIN = 2, /* RayMain.jl: colatitude, ionosphere-only density, opposite signs      */
+  RT_PRESET_SCRATCH = 3  /* scratch.jl:63-331: colatitude, psi = 3pi/2 - dip - chi, CA92          */
+} rt_preset;
+
+/* Per-ray termination class (second table).  Values are part of the ABI. */
+typedef enum rt_status {
+  RT_RUNNING = 0,          /* never returned to the caller */
+  RT_SUCCESS = 1,          /* reached t1 (SciML retcode Success)                                */
+  RT_TERMINATED_EARTH = 2, /* u[1]-re crossed zero: re_cb, RayTrace_lat.jl:303-315, _3D.jl:364-372 */
+  RT_ESCAPED = 3,          /* [EXT] r > r_esc after an accepted step (disabled when r_esc <= 0)   */
+  RT_MAX_ITERS = 4,        /* step attempts exceeded maxiters (retcode MaxIters)                  */
+  RT_DT_LESS_THAN_MIN = 5, /* rejected step shrank to <= dtmin (retcode DtLessThanMin)            */
+  RT_UNSTABLE = 6,         /* non-finite accepted state (retcode Unstable)                        */
+  RT_DT_NAN = 7            /* non-finite initial step (retcode DtNaN), e.g. rho_phi = 0 in 3D     */
+} rt_status;
+
+/* Environment: constants RayTrace_lat.jl:13-31 / RayTrace_3D.jl:38-51 and the one-off
+ * plasmasphere pre-solve RayTrace_lat.jl:21-41.  Fill with rt_env_preset(). */
+typedef struct rt_env_params {
+  int32_t preset;        /* rt_preset */
+  int32_t reserved;
+  double c, re, B0, e, me, mp, eps; /* physical constants */
+  double Lppi;           /* 5.6 - 0.46 Kp_max */
+  double Lppo;           /* argmin |ne2 - ne3| over the L grid */
+  double ne_Lppi;        /* plasmasphere density at Lppi, cm^-3 */
+  double ca_coef;        /* 0.15(cos..-0.5cos..) + 0.00127 Rbar - 0.0635 (file-specific parenthesisation) */
+  double ca_trough;      /* 5800 + 300 mlt */
+  double iono_n0;        /* 1.8e5 cm^-3 */
+  double iono_k;         /* -4.183119 */
+  double iono_h;         /* 1.0471 */
+} rt_env_params;
+
+/* Solver options: the keyword arguments of solve(), RayTrace_lat.jl:338 / RayTrace_3D.jl:395. */
+typedef struct rt_solver_opts {
+  int32_t adaptive;      /* 1 = Tsit5 + PI controller; 0 = Tsit5(), adaptive=false, dt=dt */
+  int32_t save_mode;     /* 0 = terminal state only; 1 = every accepted step (sol.t / sol[i,:]) */
+  int32_t max_samples;   /* per-ray sample capacity when save_mode = 1 (later samples dropped) */
+  int32_t save_stride;   /* keep every save_stride-th accepted step (>= 1); end point always kept */
+  int64_t maxiters;      /* step attempts (accepted + rejected); SciML default 100000 */
+  double t1;             /* tspan[2]; tspan[1] comes per ray from the launch list */
+  double dt;             /* fixed step, or initial step for adaptive (<= 0: automatic) */
+  double reltol, abstol; /* 1e-7 / 1e-6 (2D call), 1e-3 / 1e-6 (3D defaults) */
+  double dtmax, dtmin;   /* 1e6 / 1e-8 (2D call); <= 0 means t1 - t0 / 0 */
+  double r_esc;          /* [EXT] escape radius in metres, <= 0 disables */
+  int32_t slice_attempts;/* step attempts per kernel launch between compactions (0 = default) */
+  int32_t reserved;
+} rt_solver_opts;
+
+/* Caller-allocated structure-of-arrays result.  dim = 4 (2D) or 7 (3D). */
+typedef struct rt_result {
+  double *u_end;         /* [dim][n] terminal state, component-major */
+  double *t_end;         /* [n] */
+  double *group_delay;   /* [n] 2D: u4_end - f0 (RayTrace_lat.jl:257,273); 3D: u7 (RayTrace_3D.jl:356) */
+  int32_t *status;       /* [n] rt_status */
+  int32_t *naccept;      /* [n] accepted steps */
+  int32_t *nreject;      /* [n] rejected steps */
+  int32_t *nfe;          /* [n] haselgrove! evaluations */
+  int32_t *nreflect;     /* [n] [EXT] sign changes of d(latitude)/dt between accepted steps */
+} rt_result;
+
+typedef struct rt_ctx rt_ctx;
+
+/* ---- context ------------------------------------------------------------------------------ */
+RT_API int rt_create(rt_ctx **ctx, int device);
+RT_API void rt_destroy(rt_ctx *ctx);
+RT_API const char *rt_last_error(const rt_ctx *ctx); /* ctx may be NULL: last global error */
+RT_API int rt_set_env(rt_ctx *ctx, const rt_env_params *env);
+RT_API int rt_set_solver(rt_ctx *ctx, const rt_solver_opts *opts);
+/* use an existing CUDA stream (cudaStream_t as void*; NULL = the context's own stream) */
+RT_API int rt_set_stream(rt_ctx *ctx, void *cuda_stream);
+RT_API int rt_version(void);
+
+/* ---- environment (host side, one-off) ------------------------------------------------------- */
+/* script-top constants + pre-solve of the named file: RayTrace_lat.jl:13-41, RayTrace_3D.jl:38-52 */
+RT_API int rt_env_preset(int preset, rt_env_params *env);
+RT_API int rt_solver_preset(int preset, rt_solver_opts *opts);
+/* initialize_plasmasphere(Lppi, d, Rbar, mlt) -> Lppo, plasmasphere.jl:48-71; also returns ne_Lppi */
+RT_API int rt_initialize_plasmasphere(double Lppi, double d, double Rbar, double mlt, double re,
+                                      double *Lppo, double *ne_Lppi);
+
+/* ---- batch pointwise evaluators (host arrays, run on the GPU) ------------------------------- */
+/* phase_refractive_index(r, lam, chi, freq) -> [mu, dmudpsi], RayTrace_lat.jl:44-194 */
+RT_API int rt_phase_refractive_index_2d(rt_ctx *ctx, int64_t n, const double *r, const double *lam,
+                                        const double *chi, const double *freq, double *mu,
+                                        double *dmudpsi);
+/* refractive_index(r,th,ph,rho_r,rho_th,rho_ph,freq) -> [mu, dmudpsi, psi, Bvec], RayTrace_3D.jl:93-219.
+ * bvec is [3][n]. */
+RT_API int rt_refractive_index_3d(rt_ctx *ctx, int64_t n, const double *r, const double *th,
+                                  const double *ph, const double *rho_r, const double *rho_th,
+                                  const double *rho_ph, const double *freq, double *mu,
+                                  double *dmudpsi, double *psi, double *bvec);
+/* haselgrove!(du,u,p,t), RayTrace_lat.jl:251-296: u, du are [4][n] */
+RT_API int rt_haselgrove_2d(rt_ctx *ctx, int64_t n, const double *u, double *du);
+/* haselgrove!(du,u,p,t), RayTrace_3D.jl:327-359: u, du are [7][n], freq is p[1] per ray */
+RT_API int rt_haselgrove_3d(rt_ctx *ctx, int64_t n, const double *u, const double *freq, double *du);
+
+/* ---- the solve: ODEProblem + solve over a launch list --------------------------------------- */
+/* 2D launch list columns (r, theta, chi, f, t) as in README.md:11; RayTrace_lat.jl:333-338 */
+RT_API int rt_solve_2d(rt_ctx *ctx, int64_t n, const double *r, const double *theta,
+                       const double *chi, const double *f, const double *t0, rt_result *res);
+/* 3D launch list (r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0); RayTrace_3D.jl:390-395 */
+RT_API int rt_solve_3d(rt_ctx *ctx, int64_t n, const double *r, const double *theta,
+                       const double *phi, const double *rho_r, const double *rho_theta,
+                       const double *rho_phi, const double *T0, const double *f, const double *t0,
+                       rt_result *res);
+/* Same, with every pointer (launch list and rt_result members) in DEVICE memory; work is enqueued
+ * on the context's stream and the call returns after the stream has drained. */
+RT_API int rt_solve_2d_device(rt_ctx *ctx, int64_t n, const double *r, const double *theta,
+                              const double *chi, const double *f, const double *t0, rt_result *res);
+RT_API int rt_solve_3d_device(rt_ctx *ctx, int64_t n, const double *r, const double *theta,
+                              const double *phi, const double *rho_r, const double *rho_theta,
+                              const double *rho_phi, const double *T0, const double *f,
+                              const double *t0, rt_result *res);
+
+/* ---- trajectory output of the last solve (save_mode = 1) ------------------------------------- */
+/* columns: 2D  t, r, lam, chi, u4, mu, dmudpsi, dip, psi  (RayTrace_lat.jl:318-324,345-349) = 9
+ *          3D  t, r, th, ph, rho_r, rho_th, rho_ph, T      (RayTrace_3D.jl:333)             = 8 */
+RT_API int rt_traj_columns(const rt_ctx *ctx);
+RT_API int rt_traj_size(rt_ctx *ctx, int64_t *total_samples);
+/* offsets[n+1] (CSR), samples[total][columns] row-major */
+RT_API int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples);
+
+/* ---- instrumentation ------------------------------------------------------------------------- */
+typedef struct rt_stats {
+  int64_t kernel_launches;   /* kernels launched by the last solve */
+  int64_t slices;            /* integrate-kernel launches of the last solve */
+  double integrate_ms;       /* CUDA-event time of the integrate kernels of the last solve */
+  double total_ms;           /* CUDA-event time of the whole last solve on the stream */
+  int64_t total_nfe;         /* sum of nfe over rays of the last solve */
+} rt_stats;
+RT_API int rt_get_stats(const rt_ctx *ctx, rt_stats *stats);
+/* dependent-free DFMA throughput of this device in FLOP/s (roofline denominator) */
+RT_API int rt_measure_fp64_peak(rt_ctx *ctx, double *flops_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAYTRACE_B200_H */
