@@ -1,0 +1,390 @@
+// rt_integrate.cuh — the fused hot kernel: embedded adaptive Tsit5 + PI step control + Earth-hit event
+// + trajectory sampling around the Haselgrove RHS, one thread per ray.
+//
+// Replaces `solve(ODEProblem(haselgrove!,u0,tspan,p), ...; callback=cb)` at RayTrace_lat.jl:337-338 and
+// RayTrace_3D.jl:394-395.  The integrator semantics (OrdinaryDiffEq's Tsit5, PI controller, initial step,
+// ContinuousCallback, SavingCallback — third-party, absent from the reference tree) are restated in
+// DESIGN.md §3; the CPU oracle implements the same specification independently.
+//
+// Execution model
+//   * structure-of-arrays ray state in HBM; a launch processes the rays listed in idx_in[0..nactive);
+//   * each thread advances its ray by at most `attempts` step attempts (a "slice"), then writes the
+//     state back; rays still running are appended to idx_out by a warp-aggregated atomic, so the next
+//     launch runs on full warps again (periodic stream compaction);
+//   * the seven stage derivatives live in shared memory as k[stage][component][thread] (conflict-free,
+//     one 8-byte word per lane), which lets the stage loop stay rolled: the RHS is instantiated once;
+//   * warps leave the attempt loop as soon as no lane is running (__any_sync vote).
+#pragma once
+#include "rt_physics.cuh"
+
+#define RT_BLOCK 128
+
+struct RtDevOpts {
+  int adaptive, save_mode, max_samples, save_stride;
+  int maxiters;
+  double t1, dt, reltol, abstol, dtmax, dtmin, r_esc;
+};
+
+struct RtState {
+  long long n;
+  double *u;        // [DIM][n]  (also the caller's u_end)
+  double *k1;       // [DIM][n]  FSAL derivative
+  double *t;        // [n]       (also t_end)
+  double *h;        // [n]
+  double *qold;     // [n]
+  double *par;      // [n] 2D: launch frequency f0; 3D: wave frequency p[1]
+  int *status, *naccept, *nreject, *nfe, *nreflect;  // [n] (caller's result arrays)
+  int *sgn;         // [n] sign of d(latitude)/dt at the last accepted step
+  int *nsamp;       // [n] trajectory samples written
+  double *traj;     // [n][max_samples][NCOL]
+};
+
+template <int MODE>
+struct RtTraits {
+  static constexpr int DIM = (MODE == RT_PRESET_RAY3D) ? 7 : 4;
+  static constexpr int NCOL = (MODE == RT_PRESET_RAY3D) ? 8 : 9;
+};
+
+// Tsit5 tableau (Tsitouras 2011); row s holds a_{s+1,1..s}; row 5 = b (FSAL); BT = b - b_hat
+__constant__ double RT_A[6][6] = {
+    {0.161, 0, 0, 0, 0, 0},
+    {-0.008480655492356989, 0.335480655492357, 0, 0, 0, 0},
+    {2.8971530571054935, -6.359448489975075, 4.3622954328695815, 0, 0, 0},
+    {5.325864828439257, -11.748883564062828, 7.4955393428898365, -0.09249506636175525, 0, 0},
+    {5.86145544294642, -12.92096931784711, 8.159367898576159, -0.071584973281401, -0.028269050394068383, 0},
+    {0.09646076681806523, 0.01, 0.4798896504144996, 1.379008574103742, -3.290069515436081, 2.324710524099774}};
+__constant__ double RT_BT[7] = {-0.00178001105222577714, -0.0008164344596567469, 0.007880878010261995,
+                                -0.1447110071732629,     0.5823571654525552,     -0.45808210592918697,
+                                0.015151515151515152};
+
+// dense-output weights b_i(theta) of the free 4th-order interpolant
+__device__ __forceinline__ void rt_dense_weights(double th, double *b) {
+  double th2 = th * th;
+  b[0] = ((-1.0530884977290216 * th) * (th - 1.3299890189751412)) *
+         ((th2 - 1.4364028541716351 * th) + 0.7139816917074209);
+  b[1] = (0.1017 * th2) * ((th2 - 2.1966568338249754 * th) + 1.2949852507374631);
+  b[2] = (2.490627285651252793 * th2) * ((th2 - 2.38535645472061657 * th) + 1.57803468208092486);
+  b[3] = ((-16.54810288924490272 * (th - 1.21712927295533244)) * (th - 0.61620406037800089)) * th2;
+  b[4] = ((47.37952196281928122 * (th - 1.203071208372362603)) * (th - 0.658047292653547382)) * th2;
+  b[5] = ((-34.87065786149660974 * (th - 1.2)) * (th - 0.666666666666666667)) * th2;
+  b[6] = ((2.5 * (th - 1.0)) * (th - 0.6)) * th2;
+}
+
+template <int MODE>
+__device__ __forceinline__ void rt_rhs(const RtDevEnv &E, const double *y, double par, double *dy, RtExtras2D *ex) {
+  if (MODE == RT_PRESET_RAY3D)
+    rt_haselgrove_3d(E, y, par, dy);
+  else
+    rt_haselgrove_2d<MODE>(E, y, dy, ex);
+}
+
+// one trajectory row: (t, u[0..DIM)) and, in 2D, the save_func columns (RayTrace_lat.jl:318-324)
+template <int MODE>
+__device__ __forceinline__ void rt_traj_push(const RtState &S, const RtDevOpts &O, long long i, int &cnt, double t,
+                                             const double *u, const RtExtras2D &ex) {
+  constexpr int DIM = RtTraits<MODE>::DIM, NCOL = RtTraits<MODE>::NCOL;
+  if (cnt >= O.max_samples) return;
+  double *row = S.traj + ((size_t)i * (size_t)O.max_samples + (size_t)cnt) * NCOL;
+  row[0] = t;
+#pragma unroll
+  for (int c = 0; c < DIM; c++) row[1 + c] = u[c];
+  if (MODE != RT_PRESET_RAY3D) {
+    row[5] = ex.mu;
+    row[6] = ex.dmudpsi;
+    row[7] = ex.dip;
+    row[8] = ex.psi;
+  }
+  cnt++;
+}
+
+__device__ __forceinline__ int rt_sign(double x) { return (x > 0.0) - (x < 0.0); }
+
+template <int DIM>
+__device__ __forceinline__ double rt_rms(const double *v, const double *sk) {
+  double s = 0.0;
+#pragma unroll
+  for (int c = 0; c < DIM; c++) {
+    double q = v[c] / sk[c];
+    s = s + q * q;
+  }
+  return RT_SQRT(s / (double)DIM);
+}
+
+// Append ray i to the next launch's work list (warp-aggregated atomic).
+__device__ __forceinline__ void rt_enqueue(bool pred, int i, int *idx_out, int *count_out) {
+  unsigned m = __ballot_sync(0xffffffffu, pred);
+  if (m == 0) return;
+  int lane = threadIdx.x & 31;
+  int leader = __ffs(m) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(count_out, __popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (pred) idx_out[base + __popc(m & ((1u << lane) - 1u))] = i;
+}
+
+// ---- init: ODEProblem(haselgrove!, u0, tspan, p) + first RHS + automatic initial step -----------
+// launch columns (device pointers): 2D  L[0..4] = r, theta, chi, f, t0
+//                                   3D  L[0..8] = r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0
+struct RtLaunch {
+  const double *col[9];
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(RtDevEnv E, RtDevOpts O, RtState S, RtLaunch L,
+                                                           int *idx_out, int *count_out) {
+  constexpr int DIM = RtTraits<MODE>::DIM;
+  long long i = (long long)blockIdx.x * RT_BLOCK + threadIdx.x;
+  bool valid = i < S.n;
+  bool running = false;
+  if (valid) {
+    double u[DIM], k1[DIM], y[DIM], f1[DIM], sk[DIM];
+#pragma unroll
+    for (int c = 0; c < DIM; c++) u[c] = L.col[c][i];
+    double par = (MODE == RT_PRESET_RAY3D) ? L.col[7][i] : u[3];
+    double t0 = L.col[(MODE == RT_PRESET_RAY3D) ? 8 : 4][i];
+    RtExtras2D ex = {0, 0, 0, 0};
+    rt_rhs<MODE>(E, u, par, k1, &ex);
+    int nfe = 1, status = RT_RUNNING;
+    double h;
+    if (O.adaptive && !(O.dt > 0.0)) {
+#pragma unroll
+      for (int c = 0; c < DIM; c++) sk[c] = O.abstol + rt_abs(u[c]) * O.reltol;
+      double d0 = rt_rms<DIM>(u, sk);
+      double d1 = rt_rms<DIM>(k1, sk);
+      double dt0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * (d0 / d1);
+      if (dt0 > O.dtmax) dt0 = O.dtmax;
+      if (dt0 > O.t1 - t0) dt0 = O.t1 - t0;
+#pragma unroll
+      for (int c = 0; c < DIM; c++) y[c] = u[c] + dt0 * k1[c];
+      rt_rhs<MODE>(E, y, par, f1, nullptr);
+      nfe++;
+#pragma unroll
+      for (int c = 0; c < DIM; c++) f1[c] = f1[c] - k1[c];
+      double d2 = rt_rms<DIM>(f1, sk) / dt0;
+      double md = (d1 > d2) ? d1 : d2;
+      double dt1;
+      if (md <= 1e-15) {
+        double a = dt0 * 1e-3;
+        dt1 = (1e-6 > a) ? 1e-6 : a;
+      } else {
+        dt1 = rt_exp10(-(2.0 + rt_log10(md)) / 5.0);
+      }
+      double c100 = 100.0 * dt0;
+      h = (c100 < dt1) ? c100 : dt1;
+      if (h > O.dtmax) h = O.dtmax;
+      if (!rt_isfinite(h) || d1 != d1 || d2 != d2) {
+        status = RT_DT_NAN;
+        h = rt_nan();
+      }
+    } else {
+      h = O.dt;
+    }
+#pragma unroll
+    for (int c = 0; c < DIM; c++) {
+      S.u[(size_t)c * S.n + i] = u[c];
+      S.k1[(size_t)c * S.n + i] = k1[c];
+    }
+    S.t[i] = t0;
+    S.h[i] = h;
+    S.qold[i] = 1e-4;
+    S.par[i] = par;
+    S.status[i] = status;
+    S.naccept[i] = 0;
+    S.nreject[i] = 0;
+    S.nfe[i] = nfe;
+    S.nreflect[i] = 0;
+    S.sgn[i] = rt_sign(k1[1]);
+    int cnt = 0;
+    if (O.save_mode) rt_traj_push<MODE>(S, O, i, cnt, t0, u, ex);
+    S.nsamp[i] = cnt;
+    running = (status == RT_RUNNING);
+  }
+  rt_enqueue(running, (int)i, idx_out, count_out);
+}
+
+// ---- the slice kernel -----------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(RT_BLOCK)
+    rt_integrate_kernel(RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in, int nactive,
+                        int *idx_out, int *count_out, int attempts) {
+  constexpr int DIM = RtTraits<MODE>::DIM;
+  extern __shared__ double rt_smem[];
+#define RT_K(s, c) rt_smem[((s) * DIM + (c)) * RT_BLOCK + threadIdx.x]
+  const int j = blockIdx.x * RT_BLOCK + threadIdx.x;
+  const bool valid = j < nactive;
+  const long long i = valid ? idx_in[j] : 0;
+  const size_t n = (size_t)S.n;
+
+  double u[DIM], un[DIM], y[DIM];
+  double t = 0.0, h = 0.0, qold = 0.0, par = 0.0;
+  int naccept = 0, nreject = 0, nfe = 0, nreflect = 0, sgn_prev = 0, cnt = 0, status = RT_SUCCESS;
+  if (valid) {
+#pragma unroll
+    for (int c = 0; c < DIM; c++) {
+      u[c] = S.u[c * n + i];
+      RT_K(0, c) = S.k1[c * n + i];
+    }
+    t = S.t[i];
+    h = S.h[i];
+    qold = S.qold[i];
+    par = S.par[i];
+    naccept = S.naccept[i];
+    nreject = S.nreject[i];
+    nfe = S.nfe[i];
+    nreflect = S.nreflect[i];
+    sgn_prev = S.sgn[i];
+    cnt = S.nsamp[i];
+    status = S.status[i];
+  }
+  bool running = valid && status == RT_RUNNING;
+  RtExtras2D ex = {0, 0, 0, 0};
+
+  for (int a = 0; a < attempts; a++) {
+    if (!__any_sync(0xffffffffu, running)) break;
+    if (!running) continue;
+    if (t >= O.t1) { status = RT_SUCCESS; running = false; continue; }
+    if (naccept + nreject >= O.maxiters) { status = RT_MAX_ITERS; running = false; continue; }
+    if (h > O.dtmax) h = O.dtmax;
+    bool clipped = false;
+    if (t + h >= O.t1) { h = O.t1 - t; clipped = true; }
+
+    // stages 2..7: y = u + h * sum_j a_sj k_j (left to right), k_s = f(y)
+    for (int s = 0; s < 6; s++) {
+#pragma unroll
+      for (int c = 0; c < DIM; c++) {
+        double acc = RT_A[s][0] * RT_K(0, c);
+        for (int q = 1; q <= s; q++) acc = acc + RT_A[s][q] * RT_K(q, c);
+        y[c] = u[c] + h * acc;
+      }
+      double dy[DIM];
+      rt_rhs<MODE>(E, y, par, dy, &ex);
+#pragma unroll
+      for (int c = 0; c < DIM; c++) RT_K(s + 1, c) = dy[c];
+    }
+#pragma unroll
+    for (int c = 0; c < DIM; c++) un[c] = y[c];
+    nfe += 6;
+
+    double hnew = h;
+    if (O.adaptive) {
+      double ssum = 0.0;
+#pragma unroll
+      for (int c = 0; c < DIM; c++) {
+        double acc = RT_BT[0] * RT_K(0, c);
+#pragma unroll
+        for (int q = 1; q < 7; q++) acc = acc + RT_BT[q] * RT_K(q, c);
+        double e = h * acc;
+        double a0 = rt_abs(u[c]), a1 = rt_abs(un[c]);
+        double sk = O.abstol + ((a0 > a1) ? a0 : a1) * O.reltol;
+        double qq = e / sk;
+        ssum = ssum + qq * qq;
+      }
+      double EEst = RT_SQRT(ssum / (double)DIM);
+      if (!(EEst <= 1.0)) {  // reject (NaN included)
+        nreject++;
+        if (EEst != EEst) {
+          h = h * 0.2;
+        } else {
+          double qq = rt_pow_pos(EEst, 0.14) / 0.9;
+          h = h / ((5.0 < qq) ? 5.0 : qq);
+        }
+        if (h <= O.dtmin) { status = RT_DT_LESS_THAN_MIN; running = false; }
+        continue;
+      }
+      double q = rt_pow_pos(EEst, 0.14) / rt_pow_pos(qold, 0.08);
+      q = q / 0.9;
+      if (q > 5.0) q = 5.0;
+      if (q < 0.1) q = 0.1;
+      qold = (EEst > 1e-4) ? EEst : 1e-4;
+      hnew = h / q;
+    }
+    const double tn = clipped ? O.t1 : t + h;
+    naccept++;
+    bool finite = true;
+#pragma unroll
+    for (int c = 0; c < DIM; c++) finite = finite && rt_isfinite(un[c]);
+    if (!finite) {
+#pragma unroll
+      for (int c = 0; c < DIM; c++) u[c] = un[c];
+      t = tn;
+      status = RT_UNSTABLE;
+      running = false;
+      continue;
+    }
+    {  // re_cb: ContinuousCallback on u[1] - re
+      double g0 = u[0] - E.re, g1 = un[0] - E.re;
+      if ((g0 > 0.0 && g1 <= 0.0) || (g0 < 0.0 && g1 >= 0.0)) {
+        double lo = 0.0, hi = 1.0, b[7];
+        for (int it = 0; it < 52; it++) {
+          double mid = 0.5 * (lo + hi);
+          rt_dense_weights(mid, b);
+          double sacc = b[0] * RT_K(0, 0);
+#pragma unroll
+          for (int q = 1; q < 7; q++) sacc = sacc + b[q] * RT_K(q, 0);
+          double gm = (u[0] + h * sacc) - E.re;
+          bool same = (g0 > 0.0) ? (gm > 0.0) : (gm < 0.0);
+          if (same) lo = mid; else hi = mid;
+        }
+        rt_dense_weights(lo, b);
+#pragma unroll
+        for (int c = 0; c < DIM; c++) {
+          double sacc = b[0] * RT_K(0, c);
+#pragma unroll
+          for (int q = 1; q < 7; q++) sacc = sacc + b[q] * RT_K(q, c);
+          y[c] = u[c] + h * sacc;
+        }
+        t = t + lo * h;
+#pragma unroll
+        for (int c = 0; c < DIM; c++) u[c] = y[c];
+        status = RT_TERMINATED_EARTH;
+        running = false;
+        if (O.save_mode) {
+          if (MODE != RT_PRESET_RAY3D) {
+            RtMu m = rt_phase_refractive_index_2d<(MODE == RT_PRESET_RAY3D) ? RT_PRESET_LAT2D : MODE>(
+                E, u[0], u[1], u[2], u[3], &ex.dip, &ex.psi);
+            ex.mu = m.mu;
+            ex.dmudpsi = m.dmudpsi;
+          }
+          rt_traj_push<MODE>(S, O, i, cnt, t, u, ex);
+        }
+        continue;
+      }
+    }
+    t = tn;
+#pragma unroll
+    for (int c = 0; c < DIM; c++) {
+      u[c] = un[c];
+      RT_K(0, c) = RT_K(6, c);
+    }
+    int sgn = rt_sign(RT_K(0, 1));
+    if (sgn != 0 && sgn_prev != 0 && sgn != sgn_prev) nreflect++;
+    if (sgn != 0) sgn_prev = sgn;
+    const bool escaped = (O.r_esc > 0.0 && u[0] > O.r_esc);
+    if (O.save_mode) {
+      bool last = (t >= O.t1) || escaped;
+      if ((naccept % O.save_stride) == 0 || last) rt_traj_push<MODE>(S, O, i, cnt, t, u, ex);
+    }
+    if (escaped) { status = RT_ESCAPED; running = false; continue; }
+    h = hnew;
+  }
+
+  if (valid) {
+#pragma unroll
+    for (int c = 0; c < DIM; c++) {
+      S.u[c * n + i] = u[c];
+      S.k1[c * n + i] = RT_K(0, c);
+    }
+    S.t[i] = t;
+    S.h[i] = h;
+    S.qold[i] = qold;
+    S.naccept[i] = naccept;
+    S.nreject[i] = nreject;
+    S.nfe[i] = nfe;
+    S.nreflect[i] = nreflect;
+    S.sgn[i] = sgn_prev;
+    S.nsamp[i] = cnt;
+    S.status[i] = status;
+  }
+  rt_enqueue(running, (int)i, idx_out, count_out);
+#undef RT_K
+}

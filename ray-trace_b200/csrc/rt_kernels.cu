@@ -1,0 +1,736 @@
+// rt_kernels.cu — C-ABI implementation (include/raytrace_b200.h) over the sm_100a kernels.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
+// There is no CPU fallback anywhere in this file: every compute entry point launches a kernel.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "rt_integrate.cuh"
+
+#define RT_VERSION_NUM 100
+
+static thread_local std::string g_last_error;
+
+struct rt_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;      // stream in use
+  cudaStream_t own_stream = nullptr;  // created by rt_create
+  rt_env_params env{};
+  rt_solver_opts opts{};
+  RtDevEnv denv{};
+  std::string err;
+  // work buffers (device), grown on demand
+  size_t cap_rays = 0;
+  int cap_dim = 0;
+  double *k1 = nullptr, *h = nullptr, *qold = nullptr, *par = nullptr;
+  int *sgn = nullptr, *nsamp = nullptr, *idx[2] = {nullptr, nullptr}, *count = nullptr;
+  double *traj = nullptr;
+  size_t traj_bytes = 0;
+  int *h_count = nullptr;  // pinned
+  // staging buffers for the host-pointer API
+  double *stage_d = nullptr;
+  size_t stage_bytes = 0;
+  int *stage_i = nullptr;
+  size_t stage_i_bytes = 0;
+  // last solve
+  long long last_n = 0;
+  int last_mode = -1, last_max_samples = 0;
+  rt_stats stats{};
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+
+static int set_err(rt_ctx *ctx, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  if (ctx) ctx->err = buf;
+  return code;
+}
+
+#define RT_CUDA(ctx, call)                                                                        \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return set_err(ctx, RT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                     __LINE__);                                                                   \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------------
+// Host-side environment: script-top constants and the Lppo pre-solve (RayTrace_lat.jl:13-41).
+// Uses the host build of rt_math.h so that the constants are the same bits the kernels would compute.
+// ---------------------------------------------------------------------------------------------------
+static double host_ca_coef(int preset, double d, double Rbar) {
+  if (preset == RT_PRESET_RAY3D) {  // RayTrace_3D.jl:109 parenthesisation
+    double c1 = rt_cos((2.0 * RT_PI) * (d + 9.0)) / 365.0;
+    double c2 = (0.5 * rt_cos((4.0 * RT_PI) * (d + 9.0))) / 365.0;
+    return ((0.15 * (c1 - c2)) + 0.00127 * Rbar) - 0.0635;
+  }
+  double c1 = rt_cos(((2.0 * RT_PI) * (d + 9.0)) / 365.0);  // RayTrace_lat.jl:73
+  double c2 = rt_cos(((4.0 * RT_PI) * (d + 9.0)) / 365.0);
+  return ((0.15 * (c1 - 0.5 * c2)) + 0.00127 * Rbar) - 0.0635;
+}
+
+extern "C" int rt_initialize_plasmasphere(double Lppi, double d, double Rbar, double mlt, double re, double *Lppo,
+                                          double *ne_Lppi) {
+  if (!(re > 0.0)) return set_err(nullptr, RT_ERR_INVALID, "rt_initialize_plasmasphere: re must be > 0");
+  double coef = host_ca_coef(RT_PRESET_LAT2D, d, Rbar);
+  double neL = rt_exp10((-0.3145 * Lppi + 3.9043) + coef * rt_exp((2.0 - Lppi) / 1.5));  // :33
+  double span = (10.0 * re - re) / 1000.0;
+  long npts = (long)span + 1;  // re:1000:(10*re)
+  double best = 0.0, Lbest = 0.0;
+  for (long k = 0; k < npts; k++) {
+    double r = re + 1000.0 * (double)k;
+    double L = r / re;                                                    // cos(0)^2 = 1, :24
+    double ne2 = neL * rt_exp10((-1.0 * (L - Lppi)) / 0.1);               // :37
+    double ne3 = (5800.0 + 300.0 * mlt) * rt_pow_m4p5(L) + (1.0 - rt_exp((2.0 - L) / 10.0));  // :38
+    double a = rt_abs(ne2 - ne3);
+    if (k == 0 || a < best) {  // findmin keeps the first minimum, :40
+      best = a;
+      Lbest = L;
+    }
+  }
+  if (Lppo) *Lppo = Lbest;
+  if (ne_Lppi) *ne_Lppi = neL;
+  return RT_OK;
+}
+
+extern "C" int rt_env_preset(int preset, rt_env_params *env) {
+  if (!env || preset < 0 || preset > 3) return set_err(nullptr, RT_ERR_INVALID, "rt_env_preset: bad preset %d", preset);
+  memset(env, 0, sizeof(*env));
+  env->preset = preset;
+  env->c = 2.99792458e8;
+  env->re = 6.3712e6;
+  env->B0 = (preset == RT_PRESET_RAY3D) ? 3.12e-5 : 3.0696381e-5;  // RayTrace_3D.jl:40 vs RayTrace_lat.jl:15
+  env->e = 1.602e-19;
+  env->me = 9.1093e-31;
+  env->mp = 1.6726219e-27;
+  env->eps = 8.854e-12;
+  const double Kp_max = 3.0, d = 0.0, Rbar = 90.0, mlt = 2.0;  // RayTrace_lat.jl:26-31
+  env->Lppi = 5.6 - 0.46 * Kp_max;
+  rt_initialize_plasmasphere(env->Lppi, d, Rbar, mlt, env->re, &env->Lppo, &env->ne_Lppi);
+  env->ca_coef = host_ca_coef(preset, d, Rbar);
+  env->ca_trough = 5800.0 + 300.0 * mlt;
+  env->iono_n0 = 1.8e5;  // RayTrace_lat.jl:70
+  env->iono_k = -4.183119;
+  env->iono_h = 1.0471;
+  return RT_OK;
+}
+
+extern "C" int rt_solver_preset(int preset, rt_solver_opts *o) {
+  if (!o || preset < 0 || preset > 3) return set_err(nullptr, RT_ERR_INVALID, "rt_solver_preset: bad preset %d", preset);
+  memset(o, 0, sizeof(*o));
+  o->adaptive = 1;
+  o->save_mode = 0;
+  o->max_samples = 0;
+  o->save_stride = 1;
+  o->maxiters = 100000;  // SciML default
+  o->t1 = (preset == RT_PRESET_SCRATCH) ? 5.0e10 : 5.0e9;  // scratch.jl:390 / RayTrace_lat.jl:335
+  o->dt = 0.0;
+  o->abstol = 1e-6;
+  if (preset == RT_PRESET_RAY3D) {  // solve(prob, callback=cb): library defaults, RayTrace_3D.jl:395
+    o->reltol = 1e-3;
+    o->dtmax = 0.0;
+    o->dtmin = 0.0;
+  } else if (preset == RT_PRESET_LAT2D) {  // RayTrace_lat.jl:338
+    o->reltol = 1e-7;
+    o->dtmax = 1e6;
+    o->dtmin = 1e-8;
+  } else {  // RayMain.jl:387, scratch.jl:393: reltol only
+    o->reltol = 1e-7;
+    o->dtmax = 0.0;
+    o->dtmin = 0.0;
+  }
+  o->r_esc = 0.0;
+  o->slice_attempts = 0;
+  return RT_OK;
+}
+
+static void make_dev_env(const rt_env_params &e, RtDevEnv &d) {
+  d.c = e.c;
+  d.re = e.re;
+  d.B0 = e.B0;
+  d.e = e.e;
+  d.me = e.me;
+  d.mp = e.mp;
+  d.re3 = (e.re * e.re) * e.re;
+  d.e2 = e.e * e.e;
+  d.eps_me = e.eps * e.me;
+  d.eps_mp = e.eps * e.mp;
+  d.Lppi = e.Lppi;
+  d.Lppo = e.Lppo;
+  d.ne_Lppi = e.ne_Lppi;
+  d.ca_coef = e.ca_coef;
+  d.ca_trough = e.ca_trough;
+  d.iono_n0 = e.iono_n0;
+  d.iono_k = e.iono_k;
+  d.iono_h = e.iono_h;
+}
+
+static RtDevOpts make_dev_opts(const rt_solver_opts &o) {
+  RtDevOpts d;
+  d.adaptive = o.adaptive;
+  d.save_mode = o.save_mode && o.max_samples > 0;
+  d.max_samples = o.max_samples;
+  d.save_stride = o.save_stride > 0 ? o.save_stride : 1;
+  long long mi = o.maxiters > 0 ? o.maxiters : 100000;
+  d.maxiters = mi > 2000000000LL ? 2000000000 : (int)mi;
+  d.t1 = o.t1;
+  d.dt = o.dt;
+  d.reltol = o.reltol;
+  d.abstol = o.abstol;
+  d.dtmax = o.dtmax > 0.0 ? o.dtmax : std::numeric_limits<double>::infinity();
+  d.dtmin = o.dtmin > 0.0 ? o.dtmin : 0.0;
+  d.r_esc = o.r_esc;
+  return d;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Context
+// ---------------------------------------------------------------------------------------------------
+extern "C" int rt_version(void) { return RT_VERSION_NUM; }
+
+extern "C" const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+extern "C" int rt_create(rt_ctx **out, int device) {
+  if (!out) return set_err(nullptr, RT_ERR_INVALID, "rt_create: null output pointer");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return set_err(nullptr, RT_ERR_NO_DEVICE,
+                   "rt_create: no CUDA device available (%s); this library has no CPU fallback",
+                   e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (device < 0 || device >= ndev) return set_err(nullptr, RT_ERR_INVALID, "rt_create: device %d of %d", device, ndev);
+  rt_ctx *ctx = new rt_ctx();
+  ctx->device = device;
+  RT_CUDA(ctx, cudaSetDevice(device));
+  RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+  ctx->stream = ctx->own_stream;
+  for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&ctx->ev[k]));
+  RT_CUDA(ctx, cudaMallocHost(&ctx->h_count, sizeof(int)));
+  RT_CUDA(ctx, cudaMalloc(&ctx->count, sizeof(int)));
+  rt_env_preset(RT_PRESET_LAT2D, &ctx->env);
+  rt_solver_preset(RT_PRESET_LAT2D, &ctx->opts);
+  make_dev_env(ctx->env, ctx->denv);
+  *out = ctx;
+  return RT_OK;
+}
+
+static void free_work(rt_ctx *ctx) {
+  cudaFree(ctx->k1);
+  cudaFree(ctx->h);
+  cudaFree(ctx->qold);
+  cudaFree(ctx->par);
+  cudaFree(ctx->sgn);
+  cudaFree(ctx->nsamp);
+  cudaFree(ctx->idx[0]);
+  cudaFree(ctx->idx[1]);
+  ctx->k1 = ctx->h = ctx->qold = ctx->par = nullptr;
+  ctx->sgn = ctx->nsamp = ctx->idx[0] = ctx->idx[1] = nullptr;
+  ctx->cap_rays = 0;
+  ctx->cap_dim = 0;
+}
+
+extern "C" void rt_destroy(rt_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  free_work(ctx);
+  cudaFree(ctx->traj);
+  cudaFree(ctx->count);
+  cudaFree(ctx->stage_d);
+  cudaFree(ctx->stage_i);
+  cudaFreeHost(ctx->h_count);
+  for (int k = 0; k < 4; k++)
+    if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+}
+
+extern "C" int rt_set_env(rt_ctx *ctx, const rt_env_params *env) {
+  if (!ctx || !env) return set_err(ctx, RT_ERR_INVALID, "rt_set_env: null argument");
+  if (env->preset < 0 || env->preset > 3) return set_err(ctx, RT_ERR_INVALID, "rt_set_env: bad preset %d", env->preset);
+  ctx->env = *env;
+  make_dev_env(ctx->env, ctx->denv);
+  return RT_OK;
+}
+
+extern "C" int rt_set_solver(rt_ctx *ctx, const rt_solver_opts *o) {
+  if (!ctx || !o) return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: null argument");
+  if (!o->adaptive && !(o->dt > 0.0)) return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: fixed-step mode needs dt > 0");
+  if (o->adaptive && !(o->reltol > 0.0 || o->abstol > 0.0))
+    return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: adaptive mode needs a tolerance");
+  if (o->save_mode && o->max_samples <= 0)
+    return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: save_mode=1 needs max_samples > 0");
+  ctx->opts = *o;
+  return RT_OK;
+}
+
+extern "C" int rt_set_stream(rt_ctx *ctx, void *s) {
+  if (!ctx) return set_err(ctx, RT_ERR_INVALID, "rt_set_stream: null context");
+  ctx->stream = s ? (cudaStream_t)s : ctx->own_stream;
+  return RT_OK;
+}
+
+extern "C" int rt_get_stats(const rt_ctx *ctx, rt_stats *st) {
+  if (!ctx || !st) return set_err(nullptr, RT_ERR_INVALID, "rt_get_stats: null argument");
+  *st = ctx->stats;
+  return RT_OK;
+}
+
+static int ensure_stage(rt_ctx *ctx, size_t dbytes, size_t ibytes) {
+  if (dbytes > ctx->stage_bytes) {
+    cudaFree(ctx->stage_d);
+    ctx->stage_d = nullptr;
+    ctx->stage_bytes = 0;
+    RT_CUDA(ctx, cudaMalloc(&ctx->stage_d, dbytes));
+    ctx->stage_bytes = dbytes;
+  }
+  if (ibytes > ctx->stage_i_bytes) {
+    cudaFree(ctx->stage_i);
+    ctx->stage_i = nullptr;
+    ctx->stage_i_bytes = 0;
+    RT_CUDA(ctx, cudaMalloc(&ctx->stage_i, ibytes));
+    ctx->stage_i_bytes = ibytes;
+  }
+  return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Batch pointwise evaluators
+// ---------------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void rt_mu2d_kernel(RtDevEnv E, long long n, const double *r, const double *th, const double *chi,
+                               const double *f, double *mu, double *dmu) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  RtMu m = rt_phase_refractive_index_2d<MODE>(E, r[i], th[i], chi[i], f[i], nullptr, nullptr);
+  mu[i] = m.mu;
+  dmu[i] = m.dmudpsi;
+}
+
+__global__ void rt_mu3d_kernel(RtDevEnv E, long long n, const double *in /*[7][n]*/, double *out /*[6][n]*/) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  RtGeo3D g;
+  rt_geo3d(E, in[i], in[n + i], in[3 * n + i], in[4 * n + i], in[5 * n + i], g);
+  RtMu m = rt_stix<true>(g.p, (2.0 * RT_PI) * in[6 * n + i]);
+  out[i] = m.mu;
+  out[n + i] = m.dmudpsi;
+  out[2 * n + i] = g.psi;
+  out[3 * n + i] = g.Br;
+  out[4 * n + i] = g.Bt;
+  out[5 * n + i] = g.Bp;
+}
+
+template <int MODE>
+__global__ void rt_rhs_kernel(RtDevEnv E, long long n, const double *u, const double *freq, double *du) {
+  constexpr int DIM = RtTraits<MODE>::DIM;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double y[DIM], dy[DIM];
+#pragma unroll
+  for (int c = 0; c < DIM; c++) y[c] = u[(size_t)c * n + i];
+  double par = (MODE == RT_PRESET_RAY3D) ? freq[i] : y[3];
+  rt_rhs<MODE>(E, y, par, dy, nullptr);
+#pragma unroll
+  for (int c = 0; c < DIM; c++) du[(size_t)c * n + i] = dy[c];
+}
+
+static inline unsigned grid_for(long long n, int block) { return (unsigned)((n + block - 1) / block); }
+
+extern "C" int rt_phase_refractive_index_2d(rt_ctx *ctx, int64_t n, const double *r, const double *lam,
+                                            const double *chi, const double *freq, double *mu, double *dmudpsi) {
+  if (!ctx || n < 0 || (n > 0 && (!r || !lam || !chi || !freq || !mu || !dmudpsi)))
+    return set_err(ctx, RT_ERR_INVALID, "rt_phase_refractive_index_2d: bad argument");
+  if (ctx->env.preset == RT_PRESET_RAY3D)
+    return set_err(ctx, RT_ERR_INVALID, "rt_phase_refractive_index_2d: environment preset is 3D");
+  if (n == 0) return RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  size_t nb = (size_t)n * sizeof(double);
+  if (int rc = ensure_stage(ctx, 6 * nb, 0)) return rc;
+  double *d = ctx->stage_d;
+  const double *src[4] = {r, lam, chi, freq};
+  for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaMemcpyAsync(d + k * n, src[k], nb, cudaMemcpyHostToDevice, ctx->stream));
+  unsigned g = grid_for(n, 128);
+  switch (ctx->env.preset) {
+    case RT_PRESET_LAT2D:
+      rt_mu2d_kernel<RT_PRESET_LAT2D><<<g, 128, 0, ctx->stream>>>(ctx->denv, n, d, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n);
+      break;
+    case RT_PRESET_RAYMAIN:
+      rt_mu2d_kernel<RT_PRESET_RAYMAIN><<<g, 128, 0, ctx->stream>>>(ctx->denv, n, d, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n);
+      break;
+    default:
+      rt_mu2d_kernel<RT_PRESET_SCRATCH><<<g, 128, 0, ctx->stream>>>(ctx->denv, n, d, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n);
+      break;
+  }
+  RT_CUDA(ctx, cudaGetLastError());
+  RT_CUDA(ctx, cudaMemcpyAsync(mu, d + 4 * n, nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaMemcpyAsync(dmudpsi, d + 5 * n, nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
+extern "C" int rt_refractive_index_3d(rt_ctx *ctx, int64_t n, const double *r, const double *th, const double *ph,
+                                      const double *rho_r, const double *rho_th, const double *rho_ph,
+                                      const double *freq, double *mu, double *dmudpsi, double *psi, double *bvec) {
+  if (!ctx || n < 0 || (n > 0 && (!r || !th || !ph || !rho_r || !rho_th || !rho_ph || !freq || !mu || !dmudpsi || !psi || !bvec)))
+    return set_err(ctx, RT_ERR_INVALID, "rt_refractive_index_3d: bad argument");
+  if (ctx->env.preset != RT_PRESET_RAY3D)
+    return set_err(ctx, RT_ERR_INVALID, "rt_refractive_index_3d: environment preset is not RT_PRESET_RAY3D");
+  if (n == 0) return RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  size_t nb = (size_t)n * sizeof(double);
+  if (int rc = ensure_stage(ctx, 13 * nb, 0)) return rc;
+  double *d = ctx->stage_d;
+  const double *src[7] = {r, th, ph, rho_r, rho_th, rho_ph, freq};
+  for (int k = 0; k < 7; k++) RT_CUDA(ctx, cudaMemcpyAsync(d + k * n, src[k], nb, cudaMemcpyHostToDevice, ctx->stream));
+  rt_mu3d_kernel<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->denv, n, d, d + 7 * n);
+  RT_CUDA(ctx, cudaGetLastError());
+  double *o = d + 7 * n;
+  RT_CUDA(ctx, cudaMemcpyAsync(mu, o, nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaMemcpyAsync(dmudpsi, o + n, nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaMemcpyAsync(psi, o + 2 * n, nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaMemcpyAsync(bvec, o + 3 * n, 3 * nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
+static int haselgrove_batch(rt_ctx *ctx, int64_t n, const double *u, const double *freq, double *du, bool want3d) {
+  if (!ctx || n < 0 || (n > 0 && (!u || !du || (want3d && !freq))))
+    return set_err(ctx, RT_ERR_INVALID, "rt_haselgrove: bad argument");
+  const int preset = ctx->env.preset;
+  if ((preset == RT_PRESET_RAY3D) != want3d)
+    return set_err(ctx, RT_ERR_INVALID, "rt_haselgrove: environment preset %d does not match the %s call", preset,
+                   want3d ? "3D" : "2D");
+  if (n == 0) return RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int dim = want3d ? 7 : 4;
+  size_t nb = (size_t)n * sizeof(double);
+  if (int rc = ensure_stage(ctx, (2 * dim + 1) * nb, 0)) return rc;
+  double *d = ctx->stage_d;
+  RT_CUDA(ctx, cudaMemcpyAsync(d, u, dim * nb, cudaMemcpyHostToDevice, ctx->stream));
+  if (want3d) RT_CUDA(ctx, cudaMemcpyAsync(d + dim * n, freq, nb, cudaMemcpyHostToDevice, ctx->stream));
+  double *dfreq = d + dim * n, *ddu = d + (dim + 1) * n;
+  unsigned g = grid_for(n, 128);
+  switch (preset) {
+    case RT_PRESET_LAT2D: rt_rhs_kernel<RT_PRESET_LAT2D><<<g, 128, 0, ctx->stream>>>(ctx->denv, n, d, dfreq, ddu); break;
+    case RT_PRESET_RAY3D: rt_rhs_kernel<RT_PRESET_RAY3D><<<g, 128, 0, ctx->stream>>>(ctx->denv, n, d, dfreq, ddu); break;
+    case RT_PRESET_RAYMAIN: rt_rhs_kernel<RT_PRESET_RAYMAIN><<<g, 128, 0, ctx->stream>>>(ctx->denv, n, d, dfreq, ddu); break;
+    default: rt_rhs_kernel<RT_PRESET_SCRATCH><<<g, 128, 0, ctx->stream>>>(ctx->denv, n, d, dfreq, ddu); break;
+  }
+  RT_CUDA(ctx, cudaGetLastError());
+  RT_CUDA(ctx, cudaMemcpyAsync(du, ddu, dim * nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
+extern "C" int rt_haselgrove_2d(rt_ctx *ctx, int64_t n, const double *u, double *du) {
+  return haselgrove_batch(ctx, n, u, nullptr, du, false);
+}
+extern "C" int rt_haselgrove_3d(rt_ctx *ctx, int64_t n, const double *u, const double *freq, double *du) {
+  return haselgrove_batch(ctx, n, u, freq, du, true);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// The solve
+// ---------------------------------------------------------------------------------------------------
+static int ensure_work(rt_ctx *ctx, size_t n, int dim, const RtDevOpts &O, int ncol) {
+  if (n > ctx->cap_rays || dim > ctx->cap_dim) {
+    free_work(ctx);
+    size_t cap = n;
+    RT_CUDA(ctx, cudaMalloc(&ctx->k1, cap * dim * sizeof(double)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->h, cap * sizeof(double)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->qold, cap * sizeof(double)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->par, cap * sizeof(double)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->sgn, cap * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->nsamp, cap * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->idx[0], cap * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->idx[1], cap * sizeof(int)));
+    ctx->cap_rays = cap;
+    ctx->cap_dim = dim;
+  }
+  size_t tb = O.save_mode ? n * (size_t)O.max_samples * ncol * sizeof(double) : 0;
+  if (tb > ctx->traj_bytes) {
+    cudaFree(ctx->traj);
+    ctx->traj = nullptr;
+    ctx->traj_bytes = 0;
+    RT_CUDA(ctx, cudaMalloc(&ctx->traj, tb));
+    ctx->traj_bytes = tb;
+  }
+  return RT_OK;
+}
+
+__global__ void rt_group_delay_kernel(long long n, const double *u_last, const double *par, int is3d, double *gd) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  gd[i] = is3d ? u_last[i] : (u_last[i] - par[i]);  // RayTrace_3D.jl:356 / RayTrace_lat.jl:257,273
+}
+
+template <int MODE>
+static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_result &R) {
+  constexpr int DIM = RtTraits<MODE>::DIM, NCOL = RtTraits<MODE>::NCOL;
+  RtDevOpts O = make_dev_opts(ctx->opts);
+  if (int rc = ensure_work(ctx, (size_t)n, DIM, O, NCOL)) return rc;
+  RtState S;
+  S.n = n;
+  S.u = R.u_end;
+  S.k1 = ctx->k1;
+  S.t = R.t_end;
+  S.h = ctx->h;
+  S.qold = ctx->qold;
+  S.par = ctx->par;
+  S.status = R.status;
+  S.naccept = R.naccept;
+  S.nreject = R.nreject;
+  S.nfe = R.nfe;
+  S.nreflect = R.nreflect;
+  S.sgn = ctx->sgn;
+  S.nsamp = ctx->nsamp;
+  S.traj = ctx->traj;
+  cudaStream_t st = ctx->stream;
+  const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
+  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 128;
+  ctx->stats = rt_stats{};
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, sizeof(int), st));
+  int cur = 0;
+  rt_init_kernel<MODE><<<grid_for(n, RT_BLOCK), RT_BLOCK, 0, st>>>(ctx->denv, O, S, L, ctx->idx[cur], ctx->count);
+  RT_CUDA(ctx, cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
+  for (;;) {
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count, ctx->count, sizeof(int), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(ctx, cudaStreamSynchronize(st));
+    int nactive = *ctx->h_count;
+    if (nactive <= 0) break;
+    RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, sizeof(int), st));
+    rt_integrate_kernel<MODE><<<grid_for(nactive, RT_BLOCK), RT_BLOCK, smem, st>>>(
+        ctx->denv, O, S, ctx->idx[cur], nactive, ctx->idx[cur ^ 1], ctx->count, attempts);
+    RT_CUDA(ctx, cudaGetLastError());
+    cur ^= 1;
+    ctx->stats.kernel_launches++;
+    ctx->stats.slices++;
+  }
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
+  rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, R.u_end + (size_t)(DIM - 1) * n, ctx->par,
+                                                          MODE == RT_PRESET_RAY3D, R.group_delay);
+  RT_CUDA(ctx, cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
+  RT_CUDA(ctx, cudaStreamSynchronize(st));
+  float ms_int = 0, ms_tot = 0;
+  RT_CUDA(ctx, cudaEventElapsedTime(&ms_int, ctx->ev[1], ctx->ev[2]));
+  RT_CUDA(ctx, cudaEventElapsedTime(&ms_tot, ctx->ev[0], ctx->ev[3]));
+  ctx->stats.integrate_ms = ms_int;
+  ctx->stats.total_ms = ms_tot;
+  ctx->last_n = n;
+  ctx->last_mode = MODE;
+  ctx->last_max_samples = O.save_mode ? O.max_samples : 0;
+  return RT_OK;
+}
+
+static int dispatch_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_result &R) {
+  switch (ctx->env.preset) {
+    case RT_PRESET_LAT2D: return run_solve<RT_PRESET_LAT2D>(ctx, n, L, R);
+    case RT_PRESET_RAY3D: return run_solve<RT_PRESET_RAY3D>(ctx, n, L, R);
+    case RT_PRESET_RAYMAIN: return run_solve<RT_PRESET_RAYMAIN>(ctx, n, L, R);
+    default: return run_solve<RT_PRESET_SCRATCH>(ctx, n, L, R);
+  }
+}
+
+static bool result_ok(const rt_result *r) {
+  return r && r->u_end && r->t_end && r->group_delay && r->status && r->naccept && r->nreject && r->nfe && r->nreflect;
+}
+
+static int solve_common(rt_ctx *ctx, int64_t n, const double *const *cols, int ncols, rt_result *res, bool want3d,
+                        bool on_device) {
+  if (!ctx) return set_err(ctx, RT_ERR_INVALID, "rt_solve: null context");
+  if (n < 0 || n > 2000000000LL) return set_err(ctx, RT_ERR_INVALID, "rt_solve: n out of range");
+  if ((ctx->env.preset == RT_PRESET_RAY3D) != want3d)
+    return set_err(ctx, RT_ERR_INVALID, "rt_solve: environment preset %d does not match the %s call", ctx->env.preset,
+                   want3d ? "3D" : "2D");
+  if (n == 0) {
+    ctx->last_n = 0;
+    ctx->stats = rt_stats{};
+    return RT_OK;
+  }
+  if (!result_ok(res)) return set_err(ctx, RT_ERR_INVALID, "rt_solve: rt_result has null members");
+  for (int k = 0; k < ncols; k++)
+    if (!cols[k]) return set_err(ctx, RT_ERR_INVALID, "rt_solve: launch-list column %d is null", k);
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int dim = want3d ? 7 : 4;
+  RtLaunch L{};
+  if (on_device) {
+    for (int k = 0; k < ncols; k++) L.col[k] = cols[k];
+    return dispatch_solve(ctx, n, L, *res);
+  }
+  // host buffers: stage launch list and results in device memory
+  const size_t nb = (size_t)n * sizeof(double);
+  if (int rc = ensure_stage(ctx, (size_t)(ncols + dim + 2) * nb, (size_t)5 * n * sizeof(int))) return rc;
+  double *d = ctx->stage_d;
+  for (int k = 0; k < ncols; k++) {
+    RT_CUDA(ctx, cudaMemcpyAsync(d + (size_t)k * n, cols[k], nb, cudaMemcpyHostToDevice, ctx->stream));
+    L.col[k] = d + (size_t)k * n;
+  }
+  rt_result D;
+  D.u_end = d + (size_t)ncols * n;
+  D.t_end = D.u_end + (size_t)dim * n;
+  D.group_delay = D.t_end + n;
+  D.status = ctx->stage_i;
+  D.naccept = D.status + n;
+  D.nreject = D.naccept + n;
+  D.nfe = D.nreject + n;
+  D.nreflect = D.nfe + n;
+  if (int rc = dispatch_solve(ctx, n, L, D)) return rc;
+  cudaStream_t st = ctx->stream;
+  RT_CUDA(ctx, cudaMemcpyAsync(res->u_end, D.u_end, dim * nb, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaMemcpyAsync(res->t_end, D.t_end, nb, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaMemcpyAsync(res->group_delay, D.group_delay, nb, cudaMemcpyDeviceToHost, st));
+  const size_t ib = (size_t)n * sizeof(int);
+  RT_CUDA(ctx, cudaMemcpyAsync(res->status, D.status, ib, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaMemcpyAsync(res->naccept, D.naccept, ib, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaMemcpyAsync(res->nreject, D.nreject, ib, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaMemcpyAsync(res->nfe, D.nfe, ib, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaMemcpyAsync(res->nreflect, D.nreflect, ib, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaStreamSynchronize(st));
+  return RT_OK;
+}
+
+extern "C" int rt_solve_2d(rt_ctx *ctx, int64_t n, const double *r, const double *theta, const double *chi,
+                           const double *f, const double *t0, rt_result *res) {
+  const double *cols[5] = {r, theta, chi, f, t0};
+  return solve_common(ctx, n, cols, 5, res, false, false);
+}
+extern "C" int rt_solve_2d_device(rt_ctx *ctx, int64_t n, const double *r, const double *theta, const double *chi,
+                                  const double *f, const double *t0, rt_result *res) {
+  const double *cols[5] = {r, theta, chi, f, t0};
+  return solve_common(ctx, n, cols, 5, res, false, true);
+}
+extern "C" int rt_solve_3d(rt_ctx *ctx, int64_t n, const double *r, const double *theta, const double *phi,
+                           const double *rho_r, const double *rho_theta, const double *rho_phi, const double *T0,
+                           const double *f, const double *t0, rt_result *res) {
+  const double *cols[9] = {r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0};
+  return solve_common(ctx, n, cols, 9, res, true, false);
+}
+extern "C" int rt_solve_3d_device(rt_ctx *ctx, int64_t n, const double *r, const double *theta, const double *phi,
+                                  const double *rho_r, const double *rho_theta, const double *rho_phi,
+                                  const double *T0, const double *f, const double *t0, rt_result *res) {
+  const double *cols[9] = {r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0};
+  return solve_common(ctx, n, cols, 9, res, true, true);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Trajectory output (sol.t / sol[i,:] / saved_mu: RayTrace_lat.jl:345-372)
+// ---------------------------------------------------------------------------------------------------
+extern "C" int rt_traj_columns(const rt_ctx *ctx) {
+  if (!ctx) return RT_ERR_INVALID;
+  return ctx->env.preset == RT_PRESET_RAY3D ? 8 : 9;
+}
+
+extern "C" int rt_traj_size(rt_ctx *ctx, int64_t *total) {
+  if (!ctx || !total) return set_err(ctx, RT_ERR_INVALID, "rt_traj_size: null argument");
+  if (ctx->last_mode < 0 || ctx->last_max_samples <= 0)
+    return set_err(ctx, RT_ERR_STATE, "rt_traj_size: the last solve did not save trajectories (save_mode = 0)");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::vector<int> ns((size_t)ctx->last_n);
+  RT_CUDA(ctx, cudaMemcpyAsync(ns.data(), ctx->nsamp, ns.size() * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  int64_t s = 0;
+  for (int v : ns) s += v;
+  *total = s;
+  return RT_OK;
+}
+
+// gather rows [n][cap][ncol] -> packed [total][ncol] using CSR offsets
+__global__ void rt_traj_pack_kernel(long long n, int cap, int ncol, const double *traj, const long long *offsets,
+                                    double *out) {
+  long long ray = blockIdx.x;
+  long long lo = offsets[ray], cnt = offsets[ray + 1] - lo;
+  const double *src = traj + (size_t)ray * cap * ncol;
+  double *dst = out + (size_t)lo * ncol;
+  for (long long k = threadIdx.x; k < cnt * ncol; k += blockDim.x) dst[k] = src[k];
+}
+
+extern "C" int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples) {
+  if (!ctx || !offsets || !samples) return set_err(ctx, RT_ERR_INVALID, "rt_traj_copy: null argument");
+  if (ctx->last_mode < 0 || ctx->last_max_samples <= 0)
+    return set_err(ctx, RT_ERR_STATE, "rt_traj_copy: the last solve did not save trajectories (save_mode = 0)");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  const long long n = ctx->last_n;
+  const int ncol = ctx->last_mode == RT_PRESET_RAY3D ? 8 : 9;
+  std::vector<int> ns((size_t)n);
+  RT_CUDA(ctx, cudaMemcpyAsync(ns.data(), ctx->nsamp, ns.size() * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  offsets[0] = 0;
+  for (long long i = 0; i < n; i++) offsets[i + 1] = offsets[i] + ns[(size_t)i];
+  const int64_t total = offsets[n];
+  if (total == 0) return RT_OK;
+  long long *d_off = nullptr;
+  double *d_out = nullptr;
+  RT_CUDA(ctx, cudaMalloc(&d_off, (size_t)(n + 1) * sizeof(long long)));
+  cudaError_t e = cudaMalloc(&d_out, (size_t)total * ncol * sizeof(double));
+  if (e != cudaSuccess) {
+    cudaFree(d_off);
+    return set_err(ctx, RT_ERR_NOMEM, "rt_traj_copy: %s", cudaGetErrorString(e));
+  }
+  static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+  cudaMemcpyAsync(d_off, offsets, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream);
+  rt_traj_pack_kernel<<<(unsigned)n, 64, 0, ctx->stream>>>(n, ctx->last_max_samples, ncol, ctx->traj, d_off, d_out);
+  cudaMemcpyAsync(samples, d_out, (size_t)total * ncol * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+  e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d_off);
+  cudaFree(d_out);
+  if (e != cudaSuccess) return set_err(ctx, RT_ERR_CUDA, "rt_traj_copy: %s", cudaGetErrorString(e));
+  return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// FP64 roofline denominator: 8 independent DFMA chains per thread, all SMs full
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rt_dfma_peak_kernel(double *out, int iters, double a, double b) {
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int k = 0; k < iters; k++) {
+    x0 = __fma_rn(x0, a, b); x1 = __fma_rn(x1, a, b); x2 = __fma_rn(x2, a, b); x3 = __fma_rn(x3, a, b);
+    x4 = __fma_rn(x4, a, b); x5 = __fma_rn(x5, a, b); x6 = __fma_rn(x6, a, b); x7 = __fma_rn(x7, a, b);
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
+extern "C" int rt_measure_fp64_peak(rt_ctx *ctx, double *flops) {
+  if (!ctx || !flops) return set_err(ctx, RT_ERR_INVALID, "rt_measure_fp64_peak: null argument");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaDeviceProp prop;
+  RT_CUDA(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+  const int blocks = prop.multiProcessorCount * 8, iters = 1 << 14;
+  double *d = nullptr;
+  RT_CUDA(ctx, cudaMalloc(&d, (size_t)blocks * 256 * sizeof(double)));
+  double best = 0.0;
+  for (int rep = 0; rep < 5; rep++) {
+    cudaEventRecord(ctx->ev[0], ctx->stream);
+    rt_dfma_peak_kernel<<<blocks, 256, 0, ctx->stream>>>(d, iters, 0.9999999, 1e-7);
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) {
+      cudaFree(d);
+      return set_err(ctx, RT_ERR_CUDA, "rt_measure_fp64_peak: %s", cudaGetErrorString(e));
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    double fl = 2.0 * 8.0 * (double)iters * (double)blocks * 256.0 / (ms * 1e-3);
+    if (rep > 0 && fl > best) best = fl;
+  }
+  cudaFree(d);
+  *flops = best;
+  return RT_OK;
+}

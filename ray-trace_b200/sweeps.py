@@ -1,0 +1,46 @@
+"""Deterministic synthetic launch sweeps.  No RNG: plain grids, so every run and every rank
+reproduces the same launch list.  Rows follow ray_start.dat: 2D (r, θ, χ, f, t), 3D (r, θ, ϕ, ρ_r, ρ_θ, ρ_ϕ, T0, f, t)."""
+import numpy as np
+
+RE = 6.3712e6  # RayTrace_lat.jl:14
+
+
+def cfg1():
+    """The reference's own ray: u0 = [re+1e6, π/4, 0, 1000], RayTrace_lat.jl:333."""
+    return np.array([[RE + 1.0e6], [np.pi / 4], [0.0], [1000.0], [0.0]])
+
+
+def sweep_2d(n_lat=400, n_freq=250, lat_deg=(20.0, 65.0), freq_hz=(1.0e3, 3.0e4), r0=RE + 1.0e6, chi0=0.0):
+    """cfg2: launch latitude × frequency (1–30 kHz, geometric), 10^5 rays by default."""
+    lat = np.deg2rad(np.linspace(lat_deg[0], lat_deg[1], n_lat))
+    f = np.geomspace(freq_hz[0], freq_hz[1], n_freq)
+    LAT, F = np.meshgrid(lat, f, indexing="ij")
+    n = LAT.size
+    return np.ascontiguousarray(np.vstack([np.full(n, r0), LAT.ravel(), np.full(n, chi0), F.ravel(), np.zeros(n)]))
+
+
+def sweep_3d(n_colat=100, n_lon=100, n_chi=100, colat_deg=(25.0, 70.0), chi_deg=(-60.0, 60.0), alpha=0.1,
+             freq=1000.0, r0=RE + 1.0e6):
+    """cfg3/cfg5: colatitude × longitude × wave-normal angle χ; ρ = (cosχ, sinχ cosα, sinχ sinα) so that no
+    component of ρ is zero (RayTrace_3D.jl:304-310 divides by |ρ_k|); f = 1000 Hz (RayTrace_3D.jl:391)."""
+    th = np.deg2rad(np.linspace(colat_deg[0], colat_deg[1], n_colat))
+    ph = np.linspace(0.0, 2 * np.pi, n_lon, endpoint=False)
+    chi = np.deg2rad(np.linspace(chi_deg[0], chi_deg[1], n_chi))
+    TH, PH, CHI = np.meshgrid(th, ph, chi, indexing="ij")
+    n = TH.size
+    TH, PH, CHI = TH.ravel(), PH.ravel(), CHI.ravel()
+    rho = np.vstack([np.cos(CHI), np.sin(CHI) * np.cos(alpha), np.sin(CHI) * np.sin(alpha)])
+    return np.ascontiguousarray(
+        np.vstack([np.full(n, r0), TH, PH, rho, np.zeros(n), np.full(n, freq), np.zeros(n)]))
+
+
+def sweep_2d_long(n_lat=1000, n_freq=1000):
+    """cfg4: multi-bounce stress sweep, 40°–62° × 1–5 kHz; solve with t1 = 5e10 (scratch.jl:390), maxiters 1e6."""
+    return sweep_2d(n_lat, n_freq, (40.0, 62.0), (1.0e3, 5.0e3))
+
+
+def partition(n, rank, world):
+    """Contiguous launch-list partition [lo, hi) of rank `rank` out of `world`."""
+    lo = (n * rank) // world
+    hi = (n * (rank + 1)) // world
+    return lo, hi

@@ -1,0 +1,165 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle, bit for bit.
+
+Tolerances (BASELINE.json north_star): fixed-step 1e-10 relative, adaptive 1e-7 relative, termination class exact.
+Both implementations evaluate the same IEEE operations in the same order (tests assert EXACT equality, which
+implies the tolerances; the tolerance assertions are kept so that a future relaxation of exactness still has the
+contractual bound written down)."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import raytrace_b200 as R
+from raytrace_b200 import sweeps
+
+pytestmark = pytest.mark.gpu
+
+RE = 6.3712e6
+PRESETS_2D = [("lat2d", O.LAT2D), ("raymain", O.RAYMAIN), ("scratch", O.SCRATCH)]
+
+
+def _same(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    return np.array_equal(a.view(np.uint64) if a.dtype == np.float64 else a,
+                          b.view(np.uint64) if b.dtype == np.float64 else b) or (
+        a.dtype == np.float64 and np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(a[~np.isnan(a)], b[~np.isnan(b)]))
+
+
+def _points_2d(n, seed=0):
+    rng = np.random.default_rng(seed)
+    r = RE * rng.uniform(1.05, 7.0, n)
+    lam = np.deg2rad(rng.uniform(5, 80, n))
+    chi = rng.uniform(-np.pi, np.pi, n)
+    f = np.exp(rng.uniform(np.log(300.0), np.log(3e4), n))
+    return r, lam, chi, f
+
+
+@pytest.mark.parametrize("name,pid", PRESETS_2D)
+def test_phase_refractive_index_2d_bitexact(name, pid):
+    rt = R.RayTracer(name)
+    E = O.env(pid)
+    r, lam, chi, f = _points_2d(3000, 1)
+    mu, dmu = rt.phase_refractive_index(r, lam, chi, f)
+    ref = np.array([O.phase_refractive_index_2d(E, *p) for p in zip(r, lam, chi, f)])
+    assert _same(mu, ref[:, 0]) and _same(dmu, ref[:, 1])
+    rt.close()
+
+
+@pytest.mark.parametrize("name,pid", PRESETS_2D)
+def test_haselgrove_2d_bitexact(name, pid):
+    rt = R.RayTracer(name)
+    E = O.env(pid)
+    r, lam, chi, f = _points_2d(1500, 2)
+    u = np.vstack([r, lam, chi, f])
+    du = rt.haselgrove(u)
+    ref = np.array([O.haselgrove_2d(E, u[:, k]) for k in range(u.shape[1])]).T
+    assert _same(du, ref)
+    rt.close()
+
+
+def _points_3d(n, seed=3):
+    rng = np.random.default_rng(seed)
+    r = RE * rng.uniform(1.05, 7.0, n)
+    th = np.deg2rad(rng.uniform(10, 170, n))
+    ph = rng.uniform(0, 2 * np.pi, n)
+    rho = rng.normal(size=(3, n)) * rng.uniform(0.5, 100, n)
+    f = np.exp(rng.uniform(np.log(300.0), np.log(3e4), n))
+    return r, th, ph, rho, f
+
+
+def test_refractive_index_3d_bitexact():
+    rt = R.RayTracer("ray3d")
+    E = O.env(O.RAY3D)
+    r, th, ph, rho, f = _points_3d(3000)
+    mu, dmu, psi, b = rt.refractive_index(r, th, ph, rho[0], rho[1], rho[2], f)
+    ref = np.array([O.refractive_index_3d(E, r[k], th[k], ph[k], rho[0, k], rho[1, k], rho[2, k], f[k]) for k in range(r.size)])
+    assert _same(mu, ref[:, 0]) and _same(dmu, ref[:, 1]) and _same(psi, ref[:, 2]) and _same(b, ref[:, 3:6].T)
+    rt.close()
+
+
+def test_haselgrove_3d_bitexact_including_nan_lanes():
+    rt = R.RayTracer("ray3d")
+    E = O.env(O.RAY3D)
+    r, th, ph, rho, f = _points_3d(1500, 4)
+    rho[2, :10] = 0.0  # the reference's own u0 has rho_phi = 0 -> 0/0 (RayTrace_3D.jl:390, :304-310)
+    u = np.vstack([r, th, ph, rho, np.zeros_like(r)])
+    du = rt.haselgrove(u, [f])
+    ref = np.array([O.haselgrove_3d(E, u[:, k], f[k]) for k in range(r.size)]).T
+    assert np.isnan(ref[2, :10]).all()
+    assert _same(du, ref)
+    rt.close()
+
+
+def _check_solve(res, ref, rtol):
+    assert np.array_equal(res.status, ref["status"]), "termination classes differ"
+    assert np.array_equal(res.naccept, ref["naccept"]) and np.array_equal(res.nreject, ref["nreject"])
+    assert np.array_equal(res.nfe, ref["nfe"]) and np.array_equal(res.nreflect, ref["nreflect"])
+    fin = np.isfinite(ref["u_end"])
+    assert np.array_equal(fin, np.isfinite(res.u_end))
+    scale = np.maximum(np.abs(ref["u_end"][fin]), 1e-300)
+    assert np.max(np.abs(res.u_end[fin] - ref["u_end"][fin]) / scale, initial=0.0) <= rtol
+    assert _same(res.u_end, ref["u_end"]) and _same(res.t_end, ref["t_end"])
+
+
+def test_solve_2d_fixed_step_bitexact():
+    launch = sweeps.sweep_2d(16, 8)
+    rt = R.RayTracer("lat2d")
+    rt.set_solver(adaptive=0, dt=2.0e5, t1=6.0e7, maxiters=100000)
+    res = rt.solve(launch)
+    ref = O.solve_batch(O.env(O.LAT2D), O.opts(adaptive=0, dt=2.0e5, t1=6.0e7), launch, False, 8)
+    _check_solve(res, ref, 1e-10)
+    assert np.all(res.naccept == 300)
+    f0 = launch[3]
+    assert _same(res.group_delay, ref["u_end"][3] - f0)
+    rt.close()
+
+
+@pytest.mark.parametrize("name,pid", PRESETS_2D)
+def test_solve_2d_adaptive_bitexact(name, pid):
+    launch = sweeps.sweep_2d(24, 12)
+    if pid != O.LAT2D:
+        launch[1] = np.pi / 2 - launch[1]  # colatitude presets
+    rt = R.RayTracer(name)
+    rt.set_solver(adaptive=1, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, t1=4.0e8, maxiters=3000, r_esc=10 * RE,
+                  slice_attempts=37)
+    res = rt.solve(launch)
+    ref = O.solve_batch(O.env(pid), O.opts(t1=4.0e8, maxiters=3000, r_esc=10 * RE), launch, False, 8)
+    _check_solve(res, ref, 1e-7)
+    assert res.stats.slices > 1
+    rt.close()
+
+
+def test_solve_3d_adaptive_bitexact_and_statuses():
+    launch = sweeps.sweep_3d(8, 4, 10)
+    launch[5, :3] = 0.0  # DtNaN rays (rho_phi = 0)
+    rt = R.RayTracer("ray3d")
+    rt.set_solver(maxiters=5000, r_esc=10 * RE, slice_attempts=16)
+    res = rt.solve(launch)
+    ref = O.solve_batch(O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, maxiters=5000, r_esc=10 * RE), launch, True, 8)
+    _check_solve(res, ref, 1e-7)
+    assert set(np.unique(res.status)) >= {2, 7}
+    assert _same(res.group_delay, ref["u_end"][6])
+    rt.close()
+
+
+def test_trajectories_match_oracle_2d():
+    launch = sweeps.sweep_2d(4, 3)
+    rt = R.RayTracer("lat2d")
+    rt.set_solver(t1=3.0e8, save_mode=1, max_samples=512, save_stride=1)
+    res = rt.solve(launch)
+    E, o = O.env(O.LAT2D), O.opts(t1=3.0e8, save_mode=1, max_samples=512)
+    for k in range(launch.shape[1]):
+        ref = O.solve_ray_2d(E, o, launch[:4, k], launch[4, k], cap=512)
+        assert _same(res.trajectory(k), ref.traj)
+    rt.close()
+
+
+def test_trajectories_match_oracle_3d_with_stride():
+    launch = sweeps.sweep_3d(2, 2, 4)
+    rt = R.RayTracer("ray3d")
+    rt.set_solver(save_mode=1, max_samples=64, save_stride=3)
+    res = rt.solve(launch)
+    E, o = O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, save_mode=1, max_samples=64, save_stride=3)
+    for k in range(launch.shape[1]):
+        ref = O.solve_ray_3d(E, o, launch[:7, k], launch[7, k], launch[8, k], cap=64)
+        assert _same(res.trajectory(k), ref.traj)
+    rt.close()
