@@ -97,6 +97,17 @@ __device__ __forceinline__ void rt_traj_push(const RtState &S, const RtDevOpts &
   cnt++;
 }
 
+// x^p through exp(p log x), out of line: three call sites per attempt would otherwise inline exp+log each
+__device__ __noinline__ double rt_pow_dev(double x, double p) { return rt_pow_pos(x, p); }
+
+// save_func at an event point (the only sample that is not a stage point), out of line
+template <int PRESET>
+__device__ __noinline__ void rt_extras_at(const RtDevEnv &E, const double *u, RtExtras2D *ex) {
+  RtMu m = rt_phase_refractive_index_2d<PRESET>(E, u[0], u[1], u[2], u[3], &ex->dip, &ex->psi);
+  ex->mu = m.mu;
+  ex->dmudpsi = m.dmudpsi;
+}
+
 __device__ __forceinline__ int rt_sign(double x) { return (x > 0.0) - (x < 0.0); }
 
 template <int DIM>
@@ -142,22 +153,36 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(RtDevEnv E, RtDevOpts
     for (int c = 0; c < DIM; c++) u[c] = L.col[c][i];
     double par = (MODE == RT_PRESET_RAY3D) ? L.col[7][i] : u[3];
     double t0 = L.col[(MODE == RT_PRESET_RAY3D) ? 8 : 4][i];
-    RtExtras2D ex = {0, 0, 0, 0};
-    rt_rhs<MODE>(E, u, par, k1, &ex);
-    int nfe = 1, status = RT_RUNNING;
-    double h;
-    if (O.adaptive && !(O.dt > 0.0)) {
+    RtExtras2D ex = {0, 0, 0, 0}, ex1;
+    int nfe = 0, status = RT_RUNNING;
+    const bool auto_dt = O.adaptive && !(O.dt > 0.0);
+    double h = O.dt, d1 = 0.0, dt0 = 0.0;
+    // pass 0: k1 = f(u0); pass 1 (automatic initial step only): f(u0 + dt0 k1).  Rolled: one RHS instance.
+#pragma unroll 1
+    for (int pass = 0; pass < (auto_dt ? 2 : 1); pass++) {
+      if (pass == 0) {
 #pragma unroll
-      for (int c = 0; c < DIM; c++) sk[c] = O.abstol + rt_abs(u[c]) * O.reltol;
-      double d0 = rt_rms<DIM>(u, sk);
-      double d1 = rt_rms<DIM>(k1, sk);
-      double dt0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * (d0 / d1);
-      if (dt0 > O.dtmax) dt0 = O.dtmax;
-      if (dt0 > O.t1 - t0) dt0 = O.t1 - t0;
+        for (int c = 0; c < DIM; c++) y[c] = u[c];
+      } else {
 #pragma unroll
-      for (int c = 0; c < DIM; c++) y[c] = u[c] + dt0 * k1[c];
-      rt_rhs<MODE>(E, y, par, f1, nullptr);
+        for (int c = 0; c < DIM; c++) sk[c] = O.abstol + rt_abs(u[c]) * O.reltol;
+        double d0 = rt_rms<DIM>(u, sk);
+        d1 = rt_rms<DIM>(k1, sk);
+        dt0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * (d0 / d1);
+        if (dt0 > O.dtmax) dt0 = O.dtmax;
+        if (dt0 > O.t1 - t0) dt0 = O.t1 - t0;
+#pragma unroll
+        for (int c = 0; c < DIM; c++) y[c] = u[c] + dt0 * k1[c];
+      }
+      rt_rhs<MODE>(E, y, par, f1, &ex1);
       nfe++;
+      if (pass == 0) {
+        ex = ex1;
+#pragma unroll
+        for (int c = 0; c < DIM; c++) k1[c] = f1[c];
+      }
+    }
+    if (auto_dt) {
 #pragma unroll
       for (int c = 0; c < DIM; c++) f1[c] = f1[c] - k1[c];
       double d2 = rt_rms<DIM>(f1, sk) / dt0;
@@ -176,8 +201,6 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(RtDevEnv E, RtDevOpts
         status = RT_DT_NAN;
         h = rt_nan();
       }
-    } else {
-      h = O.dt;
     }
 #pragma unroll
     for (int c = 0; c < DIM; c++) {
@@ -285,13 +308,13 @@ __global__ void __launch_bounds__(RT_BLOCK)
         if (EEst != EEst) {
           h = h * 0.2;
         } else {
-          double qq = rt_pow_pos(EEst, 0.14) / 0.9;
+          double qq = rt_pow_dev(EEst, 0.14) / 0.9;
           h = h / ((5.0 < qq) ? 5.0 : qq);
         }
         if (h <= O.dtmin) { status = RT_DT_LESS_THAN_MIN; running = false; }
         continue;
       }
-      double q = rt_pow_pos(EEst, 0.14) / rt_pow_pos(qold, 0.08);
+      double q = rt_pow_dev(EEst, 0.14) / rt_pow_dev(qold, 0.08);
       q = q / 0.9;
       if (q > 5.0) q = 5.0;
       if (q < 0.1) q = 0.1;
@@ -340,10 +363,7 @@ __global__ void __launch_bounds__(RT_BLOCK)
         running = false;
         if (O.save_mode) {
           if (MODE != RT_PRESET_RAY3D) {
-            RtMu m = rt_phase_refractive_index_2d<(MODE == RT_PRESET_RAY3D) ? RT_PRESET_LAT2D : MODE>(
-                E, u[0], u[1], u[2], u[3], &ex.dip, &ex.psi);
-            ex.mu = m.mu;
-            ex.dmudpsi = m.dmudpsi;
+            rt_extras_at<(MODE == RT_PRESET_RAY3D) ? RT_PRESET_LAT2D : MODE>(E, u, &ex);
           }
           rt_traj_push<MODE>(S, O, i, cnt, t, u, ex);
         }

@@ -323,7 +323,7 @@ __global__ void rt_mu3d_kernel(RtDevEnv E, long long n, const double *in /*[7][n
   if (i >= n) return;
   RtGeo3D g;
   rt_geo3d(E, in[i], in[n + i], in[3 * n + i], in[4 * n + i], in[5 * n + i], g);
-  RtMu m = rt_stix<true>(g.p, (2.0 * RT_PI) * in[6 * n + i]);
+  RtMu m = rt_stix(g.p, (2.0 * RT_PI) * in[6 * n + i], true);
   out[i] = m.mu;
   out[n + i] = m.dmudpsi;
   out[2 * n + i] = g.psi;

@@ -39,20 +39,22 @@ struct RtMu {
   double mu, dmudpsi;
 };
 
-// CA92 plasmasphere + exponential ionosphere, cm^-3: RayTrace_lat.jl:69-83, RayTrace_3D.jl:105-119
+// CA92 plasmasphere + exponential ionosphere, cm^-3: RayTrace_lat.jl:69-83, RayTrace_3D.jl:105-119.
+// The three CA92 segments go through ONE exp and ONE exp10 call site (arguments selected per segment) to keep
+// the instruction footprint small; each lane still evaluates exactly the expression of its own segment, so
+// the bits are those of the reference's if/elseif chain.
 __device__ __forceinline__ double rt_density_cm3(const RtDevEnv &E, double r, double Lshell) {
   double ne_iono = E.iono_n0 * rt_exp(E.iono_k * ((r / E.re) - E.iono_h));
-  double ne_plasma;
-  if (Lshell <= E.Lppi) {
-    double log_ne = (-0.3145 * Lshell + 3.9043) + E.ca_coef * rt_exp((2.0 - Lshell) / 1.5);
-    ne_plasma = rt_exp10(log_ne);
-  } else if (E.Lppi < Lshell && Lshell <= E.Lppo) {
-    ne_plasma = E.ne_Lppi * rt_exp10((E.Lppi - Lshell) / 0.1);
-  } else if (E.Lppo < Lshell) {
-    ne_plasma = E.ca_trough * rt_pow_m4p5(Lshell) + (1.0 - rt_exp((2.0 - Lshell) / 10.0));
-  } else {
-    ne_plasma = 0.0;
-  }
+  const bool seg1 = Lshell <= E.Lppi;
+  const bool seg2 = E.Lppi < Lshell && Lshell <= E.Lppo;
+  const bool seg3 = E.Lppo < Lshell;
+  double ex = 0.0, p10 = 0.0;
+  if (seg1 || seg3) ex = rt_exp(seg1 ? (2.0 - Lshell) / 1.5 : (2.0 - Lshell) / 10.0);
+  if (seg1 || seg2) p10 = rt_exp10(seg1 ? (-0.3145 * Lshell + 3.9043) + E.ca_coef * ex : (E.Lppi - Lshell) / 0.1);
+  double ne_plasma = 0.0;
+  if (seg1) ne_plasma = p10;
+  if (seg2) ne_plasma = E.ne_Lppi * p10;
+  if (seg3) ne_plasma = E.ca_trough * rt_pow_m4p5(Lshell) + (1.0 - ex);
   return ne_iono + ne_plasma;
 }
 
@@ -64,8 +66,7 @@ __device__ __forceinline__ void rt_plasma_from(const RtDevEnv &E, double n_e, do
 }
 
 // Stix parameters -> mu = sqrt|mu^2_+| (and dmu/dpsi when WITH_D): RayTrace_lat.jl:96-184
-template <bool WITH_D>
-__device__ __forceinline__ RtMu rt_stix(const RtPlasma &p, double omega) {
+__device__ __forceinline__ RtMu rt_stix(const RtPlasma &p, double omega, bool with_d) {
   double w2 = omega * omega;
   double xe = p.w_e2 / w2, xp = p.w_p2 / w2;
   double R = 1.0 - xe * (omega / (omega - p.W_e)) - xp * (omega / (omega + p.W_p));
@@ -86,7 +87,7 @@ __device__ __forceinline__ RtMu rt_stix(const RtPlasma &p, double omega) {
   RtMu out;
   out.mu = RT_SQRT(rt_abs(mu2));
   out.dmudpsi = 0.0;
-  if (WITH_D) {
+  if (with_d) {
     double dA = ((2.0 * (S - P)) * s) * c;
     double dB = ((2.0 * X) * s) * c;
     double dF = (1.0 / (2.0 * F)) * ((((X * X) * 4.0) * (s2 * s)) * c - ((8.0 * (PD * PD)) * s) * c);
@@ -141,7 +142,7 @@ __device__ __forceinline__ RtMu rt_phase_refractive_index_2d(const RtDevEnv &E, 
   rt_geo2d<PRESET>(E, r, th, chi, p, dip, psi);
   if (dip_out) *dip_out = dip;
   if (psi_out) *psi_out = psi;
-  return rt_stix<true>(p, (2.0 * RT_PI) * freq);
+  return rt_stix(p, (2.0 * RT_PI) * freq, true);
 }
 
 // mu only, out of line: the rarely-taken slow path of d(mu)/dr (|r| so small that r -+ 5e-12 != r)
@@ -150,11 +151,19 @@ __device__ __noinline__ double rt_mu2d_slow(const RtDevEnv &E, double r, double 
   RtPlasma p;
   double dip, psi;
   rt_geo2d<PRESET>(E, r, th, chi, p, dip, psi);
-  return rt_stix<false>(p, (2.0 * RT_PI) * freq).mu;
+  return rt_stix(p, (2.0 * RT_PI) * freq, false).mu;
 }
 
 struct RtExtras2D {  // save_func by-products, RayTrace_lat.jl:318-324
   double mu, dmudpsi, dip, psi;
+};
+
+// The five refractive-index evaluations one RHS needs, as a ROLLED loop so that the geometry and Stix code
+// is instantiated once (the kernel has to fit the instruction cache; with the evaluations inlined side by side
+// the first profile showed "no instruction" as the top stall).  point 0 = centre (with dmu/dpsi), 1/2 =
+// theta -/+ 5e-12, 3/4 = centre medium at f -/+ 5e-6.
+struct RtFivePoint {
+  double mu_c, dmudpsi, mu_tl, mu_tr, mu_fl, mu_fr;
 };
 
 // haselgrove!(du,u,p,t) 2D: RayTrace_lat.jl:251-273 (signs: RayMain.jl:341-342)
@@ -162,29 +171,44 @@ template <int PRESET>
 __device__ __forceinline__ void rt_haselgrove_2d(const RtDevEnv &E, const double *u, double *du, RtExtras2D *ex) {
   const double r = u[0], th = u[1], chi = u[2], freq = u[3];
   const double two_pi = 2.0 * RT_PI;
-  RtPlasma pc, pl, pr;
-  double dip, psi, d0, d1;
-  rt_geo2d<PRESET>(E, r, th, chi, pc, dip, psi);
-  rt_geo2d<PRESET>(E, r, th - 1.0e-11 / 2.0, chi, pl, d0, d1);
-  rt_geo2d<PRESET>(E, r, th + 1.0e-11 / 2.0, chi, pr, d0, d1);
-  const double omega = two_pi * freq;
-  RtMu c = rt_stix<true>(pc, omega);
-  double mu_tl = rt_stix<false>(pl, omega).mu;
-  double mu_tr = rt_stix<false>(pr, omega).mu;
-  double mu_fl = rt_stix<false>(pc, two_pi * (freq - 1.0e-5 / 2.0)).mu;
-  double mu_fr = rt_stix<false>(pc, two_pi * (freq + 1.0e-5 / 2.0)).mu;
-  double dmudth = (mu_tr - mu_tl) / 1.0e-11;
-  double dmudf = (mu_fr - mu_fl) / 1.0e-5;
+  RtPlasma pc, p;
+  double dip = 0.0, psi = 0.0;
+  RtFivePoint m = {0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+  for (int k = 0; k < 5; k++) {
+    double f_k = freq;
+    if (k < 3) {
+      double th_k = (k == 0) ? th : ((k == 1) ? th - 1.0e-11 / 2.0 : th + 1.0e-11 / 2.0);
+      double d0, d1;
+      rt_geo2d<PRESET>(E, r, th_k, chi, p, d0, d1);
+      if (k == 0) {
+        pc = p;
+        dip = d0;
+        psi = d1;
+      }
+    } else {
+      p = pc;
+      f_k = (k == 3) ? freq - 1.0e-5 / 2.0 : freq + 1.0e-5 / 2.0;
+    }
+    RtMu v = rt_stix(p, two_pi * f_k, k == 0);
+    if (k == 0) { m.mu_c = v.mu; m.dmudpsi = v.dmudpsi; }
+    if (k == 1) m.mu_tl = v.mu;
+    if (k == 2) m.mu_tr = v.mu;
+    if (k == 3) m.mu_fl = v.mu;
+    if (k == 4) m.mu_fr = v.mu;
+  }
+  double dmudth = (m.mu_tr - m.mu_tl) / 1.0e-11;
+  double dmudf = (m.mu_fr - m.mu_fl) / 1.0e-5;
   double rl = r - 1.0e-11 / 2.0, rr = r + 1.0e-11 / 2.0;
   double dmudr;
   if (rl == r && rr == r) {
-    dmudr = (c.mu - c.mu) / 1.0e-11;  // 0.0, or NaN when mu is not finite
+    dmudr = (m.mu_c - m.mu_c) / 1.0e-11;  // 0.0, or NaN when mu is not finite
   } else {
     dmudr = (rt_mu2d_slow<PRESET>(E, rr, th, chi, freq) - rt_mu2d_slow<PRESET>(E, rl, th, chi, freq)) / 1.0e-11;
   }
   double sc, cc;
   rt_sincos(chi, &sc, &cc);
-  const double mu = c.mu, dmudpsi = c.dmudpsi;
+  const double mu = m.mu_c, dmudpsi = m.dmudpsi;
   if (PRESET != RT_PRESET_RAYMAIN) {
     du[0] = (1.0 / (mu * mu)) * (mu * cc + dmudpsi * sc);
     du[1] = (1.0 / (r * (mu * mu))) * (mu * sc - dmudpsi * cc);
@@ -235,7 +259,7 @@ __device__ __noinline__ double rt_mu3d_slow(const RtDevEnv &E, double r, double 
                                             double rho_p, double freq) {
   RtGeo3D g;
   rt_geo3d(E, r, th, rho_r, rho_t, rho_p, g);
-  return rt_stix<false>(g.p, (2.0 * RT_PI) * freq).mu;
+  return rt_stix(g.p, (2.0 * RT_PI) * freq, false).mu;
 }
 
 // Kimura-form d(mu)/d(rho_k), RayTrace_3D.jl:261-311; k selects the component
@@ -250,18 +274,31 @@ __device__ __forceinline__ double rt_ddrho(const RtGeo3D &g, const RtMu &c, doub
 __device__ __forceinline__ void rt_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, double *du) {
   const double r = u[0], th = u[1], rr_ = u[3], rt_ = u[4], rp_ = u[5];
   const double two_pi = 2.0 * RT_PI;
-  RtGeo3D gc, gl, gr;
-  rt_geo3d(E, r, th, rr_, rt_, rp_, gc);
-  rt_geo3d(E, r, th - 1.0e-11 / 2.0, rr_, rt_, rp_, gl);
-  rt_geo3d(E, r, th + 1.0e-11 / 2.0, rr_, rt_, rp_, gr);
-  const double omega = two_pi * freq;
-  RtMu c = rt_stix<true>(gc.p, omega);
-  double mu_tl = rt_stix<false>(gl.p, omega).mu;
-  double mu_tr = rt_stix<false>(gr.p, omega).mu;
-  double mu_fl = rt_stix<false>(gc.p, two_pi * (freq - 1.0e-5 / 2.0)).mu;
-  double mu_fr = rt_stix<false>(gc.p, two_pi * (freq + 1.0e-5 / 2.0)).mu;
-  double dmudt = (mu_tr - mu_tl) / 1.0e-11;
-  double dmudf = (mu_fr - mu_fl) / 1.0e-5;
+  RtGeo3D gc, g;
+  RtFivePoint m = {0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+  for (int k = 0; k < 5; k++) {
+    double f_k = freq;
+    if (k < 3) {
+      double th_k = (k == 0) ? th : ((k == 1) ? th - 1.0e-11 / 2.0 : th + 1.0e-11 / 2.0);
+      rt_geo3d(E, r, th_k, rr_, rt_, rp_, g);
+      if (k == 0) gc = g;
+    } else {
+      g.p = gc.p;
+      f_k = (k == 3) ? freq - 1.0e-5 / 2.0 : freq + 1.0e-5 / 2.0;
+    }
+    RtMu v = rt_stix(g.p, two_pi * f_k, k == 0);
+    if (k == 0) { m.mu_c = v.mu; m.dmudpsi = v.dmudpsi; }
+    if (k == 1) m.mu_tl = v.mu;
+    if (k == 2) m.mu_tr = v.mu;
+    if (k == 3) m.mu_fl = v.mu;
+    if (k == 4) m.mu_fr = v.mu;
+  }
+  RtMu c;
+  c.mu = m.mu_c;
+  c.dmudpsi = m.dmudpsi;
+  double dmudt = (m.mu_tr - m.mu_tl) / 1.0e-11;
+  double dmudf = (m.mu_fr - m.mu_fl) / 1.0e-5;
   double dmudp = (c.mu - c.mu) / 1.0e-11;  // mu independent of phi
   double rl = r - 1.0e-11 / 2.0, rh = r + 1.0e-11 / 2.0;
   double dmudr;

@@ -107,7 +107,7 @@ def test_solve_2d_fixed_step_bitexact():
     res = rt.solve(launch)
     ref = O.solve_batch(O.env(O.LAT2D), O.opts(adaptive=0, dt=2.0e5, t1=6.0e7), launch, False, 8)
     _check_solve(res, ref, 1e-10)
-    assert np.all(res.naccept == 300)
+    assert np.all(res.naccept[res.status == 1] == 300)
     f0 = launch[3]
     assert _same(res.group_delay, ref["u_end"][3] - f0)
     rt.close()
