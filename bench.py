@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py — RHS evaluations/s and rays/s of the batched whistler ray tracer on N B200s.
+
+Workload (config.workload): "cfg3" = BASELINE.json configs[2], the 3D (RayTrace_3D.jl) sweep of 10^6 rays over
+colatitude x longitude x wave-normal angle that north_star's target is quoted on.  At N GPUs the sweep is refined
+along longitude to N*10^6 rays and partitioned contiguously (weak scaling, no data-path collective); the one
+exchange is the gather of terminal records to rank 0 (inside the timed step for N > 1).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3|cfg2] [--impl ours|reference]
+
+A step = one full solve of the rank's launch list (init kernel + integrate slices + group-delay kernel).
+value      : RHS evaluations/s, launch list and results resident in HBM (device-pointer C-ABI entry point)
+e2e        : same metric through rt_solve_3d with pinned HOST buffers (H2D + D2H inside the timed region)
+roofline   : FP64 CUDA-core FLOP/s of the integrate kernel vs the DFMA peak measured in this run
+cpu_baseline / --impl reference : the CPU oracle (a port of the Julia path; Julia is not available) on all host cores
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+RE = 6.3712e6
+# Algorithmic FP64 work per Haselgrove RHS evaluation: executed
+# DADD + DMUL + 2*DFMA per RHS of the minimal faithful schedule, calibrated once with ncu
+# (profiles/r1_flop_calibration.md) and frozen.
+FLOP_PER_RHS = {"cfg3": 2900.0, "cfg2": 2700.0}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg2"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rays-per-gpu", type=int, default=0, help="override (testing only)")
+    ap.add_argument("--slice", type=int, default=0)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="rays in the CPU sample (0 = default)")
+    return ap.parse_args()
+
+
+def make_launch(workload, world, rank, rays_per_gpu=0):
+    """This rank's contiguous partition of the (weak-scaled) sweep; returns (launch [ncol, n_local], n_total)."""
+    from raytrace_b200 import sweeps
+    if workload == "cfg3":
+        if rays_per_gpu:
+            k = max(1, int(round((rays_per_gpu / 100.0) ** 0.5)))
+            full = sweeps.sweep_3d(k, k * world, 100)
+        else:
+            full = sweeps.sweep_3d(100, 100 * world, 100)
+    else:
+        if rays_per_gpu:
+            full = sweeps.sweep_2d(max(1, rays_per_gpu // 250) * world, 250)
+        else:
+            full = sweeps.sweep_2d(400 * world, 250)
+    n_total = full.shape[1]
+    lo, hi = sweeps.partition(n_total, rank, world)
+    return np.ascontiguousarray(full[:, lo:hi]), n_total
+
+
+def solver_kwargs(workload, slice_attempts=0):
+    """Solver options of the named config."""
+    if workload == "cfg3":  # RayTrace_3D.jl:395 defaults
+        kw = dict(adaptive=1, reltol=1e-3, abstol=1e-6, dtmax=0.0, dtmin=0.0, maxiters=100000, t1=5.0e9, r_esc=10 * RE)
+    else:  # RayTrace_lat.jl:338
+        kw = dict(adaptive=1, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, maxiters=100000, t1=5.0e9, r_esc=10 * RE)
+    if slice_attempts:
+        kw["slice_attempts"] = slice_attempts
+    return kw
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_oracle_run(workload, launch, nthreads):
+    """Time the CPU oracle (port of the Julia path) on `launch`; returns (seconds, total RHS evals, n rays)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    kw = solver_kwargs(workload)
+    kw.pop("adaptive")
+    o = O.opts(**kw)
+    E = O.env(O.RAY3D if workload == "cfg3" else O.LAT2D)
+    t = time.perf_counter()
+    out = O.solve_batch(E, o, launch, workload == "cfg3", nthreads)
+    dt = time.perf_counter() - t
+    return dt, int(out["nfe"].astype(np.int64).sum()), launch.shape[1]
+
+
+def cpu_sample(workload, launch, nrays):
+    """A bounded, strided (hence representative) sample of the rank-0 launch list."""
+    n = launch.shape[1]
+    if nrays >= n:
+        return launch
+    idx = np.linspace(0, n - 1, nrays).astype(np.int64)
+    return np.ascontiguousarray(launch[:, idx])
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path (oracle port; Julia is unavailable on this image) on all host
+    cores, each step a bounded sample of the same workload.  Rank 0 only."""
+    if rank != 0:
+        return
+    launch, _ = make_launch(args.workload, 1, 0, args.rays_per_gpu)
+    ncores = os.cpu_count() or 1
+    nsample = args.cpu_sample or (40000 if args.workload == "cfg3" else 96)
+    sample = cpu_sample(args.workload, launch, nsample)
+    for _ in range(min(args.warmup, 1)):
+        cpu_oracle_run(args.workload, cpu_sample(args.workload, launch, max(64, nsample // 20)), ncores)
+    tot_t, tot_nfe, tot_rays = 0.0, 0, 0
+    for _ in range(args.steps):
+        dt, nfe, nr = cpu_oracle_run(args.workload, sample, ncores)
+        tot_t += dt
+        tot_nfe += nfe
+        tot_rays += nr
+    val = tot_nfe / tot_t
+    desc = f"{sample.shape[1]} rays strided from the {launch.shape[1]}-ray {args.workload} launch list per step"
+    line = {
+        "impl": "reference", "metric": "rhs_evals_per_s", "value": val, "unit": "RHS evals/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "rays_per_s": tot_rays / tot_t,
+        "config": {"workload": args.workload, "rays_per_step": int(sample.shape[1]), "solver": solver_kwargs(args.workload)},
+        "cpu_baseline": {"value": val, "unit": "RHS evals/s", "cores": ncores, "kind": "port", "sample": desc},
+        "e2e": {"value": val, "unit": "RHS evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference is Julia (no julia binary here); this is the plain-C oracle port, which calls the "
+                "refractive index 12x per RHS exactly as RayTrace_3D.jl does",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import raytrace_b200 as R
+    from raytrace_b200 import multi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    launch_h, n_total = make_launch(args.workload, world, rank, args.rays_per_gpu)
+    ncol, n = launch_h.shape
+    is3d = args.workload == "cfg3"
+    dim = 7 if is3d else 4
+    rt = R.RayTracer("ray3d" if is3d else "lat2d", device=local_rank)
+    rt.set_solver(**solver_kwargs(args.workload, args.slice))
+    stream = torch.cuda.current_stream()
+    rt.set_stream(stream.cuda_stream)
+    peak = rt.measure_fp64_peak()
+
+    # device-resident launch list and results
+    launch_d = torch.from_numpy(launch_h).to(dev)
+    u_end = torch.empty((dim, n), dtype=torch.float64, device=dev)
+    t_end = torch.empty(n, dtype=torch.float64, device=dev)
+    gd = torch.empty(n, dtype=torch.float64, device=dev)
+    ints = torch.empty((5, n), dtype=torch.int32, device=dev)
+    res_ptrs = {"u_end": u_end.data_ptr(), "t_end": t_end.data_ptr(), "group_delay": gd.data_ptr(),
+                "status": ints[0].data_ptr(), "naccept": ints[1].data_ptr(), "nreject": ints[2].data_ptr(),
+                "nfe": ints[3].data_ptr(), "nreflect": ints[4].data_ptr()}
+    cols = [launch_d[k].data_ptr() for k in range(ncol)]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step_device():
+        st = rt.solve_device(n, cols, res_ptrs)
+        if world > 1:
+            d, i = multi.pack_terminal(u_end, t_end, gd, ints[0], ints[1], ints[2], ints[3], ints[4])
+            multi.gather_terminal(d, i, n_total, rank, world)
+        return st
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches, integ_ms, slices = 0, 0.0, 0
+    for k in range(args.steps):
+        flush.fill_(k & 0xFF)  # L2 flush between timed iterations (not timed)
+        barrier()
+        ev[k][0].record(stream)
+        st = step_device()
+        ev[k][1].record(stream)
+        launches += st.kernel_launches
+        integ_ms += st.integrate_ms
+        slices += st.slices
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_local = sum(a.elapsed_time(b) for a, b in ev)
+    nfe_local = int(ints[3].to(torch.int64).sum().item())
+    status_h = ints[0].cpu().numpy()
+
+    # e2e: pinned host buffers through the host-pointer entry point (H2D + D2H inside the timed region)
+    launch_p = torch.from_numpy(launch_h).pin_memory()
+    res_h = R.api.SolveResult(n, dim)
+    pinned = {}
+    for name in ("u_end", "t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
+        t = torch.from_numpy(getattr(res_h, name)).pin_memory()
+        pinned[name] = t
+        setattr(res_h, name, t.numpy())
+    cres = res_h._c()
+    fn = R.api._lib().rt_solve_3d if is3d else R.api._lib().rt_solve_2d
+    hcols = [ctypes.c_void_p(launch_p[k].data_ptr()) for k in range(ncol)]
+
+    def step_host():
+        rc = fn(rt._ctx, ctypes.c_int64(n), *hcols, ctypes.byref(cres))
+        if rc != 0:
+            raise RuntimeError(R.api._lib().rt_last_error(rt._ctx).decode())
+        if world > 1:  # host-side assembly on rank 0 is the caller's job; keep ranks in step
+            dist.barrier()
+
+    step_host()
+    barrier()
+    e2e_ms = 0.0
+    for k in range(args.steps):
+        flush.fill_(k & 0xFF)
+        barrier()
+        t0 = time.perf_counter()
+        step_host()
+        torch.cuda.synchronize()
+        e2e_ms += 1e3 * (time.perf_counter() - t0)
+    barrier()
+    h2d = ncol * n * 8
+    d2h = (dim + 2) * n * 8 + 5 * n * 4
+
+    # max over ranks / sums over ranks
+    if world > 1:
+        tmax = torch.tensor([ms_local, e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = torch.tensor([nfe_local, n, launches], dtype=torch.float64, device=dev)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms_all, e2e_all = float(tmax[0]), float(tmax[1])
+        nfe_all, rays_all, launches_all = float(tsum[0]), float(tsum[1]), float(tsum[2])
+    else:
+        ms_all, e2e_all, nfe_all, rays_all, launches_all = ms_local, e2e_ms, float(nfe_local), float(n), float(launches)
+
+    if rank == 0:
+        K = args.steps
+        value = nfe_all * K / (ms_all * 1e-3)
+        flop = FLOP_PER_RHS[args.workload]
+        # dominant kernel = rt_integrate_kernel: rank-0 figures, CUDA events inside the library on the launch stream
+        achieved = (nfe_local * K * flop) / (integ_ms * 1e-3) / 1e12
+        ncores = os.cpu_count() or 1
+        cpu = None
+        if world == 1 or True:
+            nsample = args.cpu_sample or (40000 if is3d else 96)
+            sample = cpu_sample(args.workload, launch_h, nsample)
+            cdt, cnfe, cn = cpu_oracle_run(args.workload, sample, ncores)
+            cpu = {"value": cnfe / cdt, "unit": "RHS evals/s", "cores": ncores, "kind": "port",
+                   "sample": f"{cn} rays strided from rank 0's {n}-ray launch list, {cdt:.1f} s wall",
+                   "rays_per_s": cn / cdt}
+        uniq, cnt = np.unique(status_h, return_counts=True)
+        line = {
+            "metric": "rhs_evals_per_s", "value": value, "unit": "RHS evals/s", "n_gpus": world, "steps": K,
+            "warmup": args.warmup, "ms_per_step": ms_all / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "rays_per_s": rays_all * K / (ms_all * 1e-3),
+            "config": {"workload": args.workload, "rays_total": int(rays_all), "rays_per_gpu": int(n),
+                       "rhs_evals_per_step": int(nfe_all), "solver": solver_kwargs(args.workload, args.slice),
+                       "partition": f"contiguous x{world}", "l2": "flushed between timed steps (256 MiB fill)",
+                       "status_counts_rank0": {R.STATUS_NAMES[int(a)]: int(b) for a, b in zip(uniq, cnt)}},
+            "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak / 1e12, "unit": "TFLOP/s",
+                         "frac": achieved / (peak / 1e12), "traffic": None,
+                         "peak_source": "DFMA-chain microbenchmark in this run (MEASURED_PEAKS.json has no FP64 entry)",
+                         "flop_per_rhs": flop, "kernel": "rt_integrate_kernel",
+                         "avg_launch_ms": integ_ms / max(slices, 1), "launches": int(slices)},
+            "cpu_baseline": cpu,
+            "e2e": {"value": nfe_all * K / (e2e_all * 1e-3), "unit": "RHS evals/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_all / K,
+                    "rays_per_s": rays_all * K / (e2e_all * 1e-3)},
+            "gpu_launches": int(launches_all),
+            "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    rt.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -385,3 +385,15 @@ def write_ray_start(path, launch, header=None):
         fh.write("# r theta chi f t\n" if launch.shape[0] == 5 else "# r theta phi rho_r rho_theta rho_phi T0 f t\n")
         for k in range(launch.shape[1]):
             fh.write(" ".join(repr(float(v)) for v in launch[:, k]) + "\n")
+
+
+def _solve_device(self, n, col_ptrs, res_ptrs):
+    """rt_solve_{2d,3d}_device: every pointer is a device address (ints), e.g. torch tensors' data_ptr().
+    col_ptrs: 5 (2D) or 9 (3D) launch columns; res_ptrs: dict with the rt_result member names."""
+    cres = _Result(*[C.c_void_p(res_ptrs[k]) for k, _ in _Result._fields_])
+    fn = _lib().rt_solve_3d_device if self.dim == 7 else _lib().rt_solve_2d_device
+    _check(fn(self._ctx, C.c_int64(n), *[C.c_void_p(p) for p in col_ptrs], C.byref(cres)), self._ctx)
+    return self.stats()
+
+
+RayTracer.solve_device = _solve_device
