@@ -269,7 +269,11 @@ __global__ void __launch_bounds__(RT_BLOCK)
     if (naccept + nreject >= O.maxiters) { status = RT_MAX_ITERS; running = false; continue; }
     if (h > O.dtmax) h = O.dtmax;
     bool clipped = false;
-    if (t + h >= O.t1) { h = O.t1 - t; clipped = true; }
+    {  // tstop handling: a step landing within 100 eps of t1 goes to t1 exactly
+      double tt = t + h, at = rt_abs(t), a1 = rt_abs(O.t1);
+      double tol = (100.0 * 2.220446049250313e-16) * ((at > a1) ? at : a1);
+      if (tt >= O.t1 || O.t1 - tt <= tol) { h = O.t1 - t; clipped = true; }
+    }
 
     // stages 2..7: y = u + h * sum_j a_sj k_j (left to right), k_s = f(y)
     for (int s = 0; s < 6; s++) {

@@ -15,7 +15,7 @@
  *     unbounded values (x86 and PTX disagree on out-of-range conversions).
  *
  * Accuracy (measured in tests/test_rt_math.py against mpmath): <= 1 ulp for exp, exp10, log, sin,
- * cos, atan, acos; <= 2 ulp for tan (sin/cos quotient) and log10.
+ * cos, atan, acos; <= 2 ulp for tan (sin/cos quotient) and log10; <= 4 ulp for x^-4.5.
  * Domain note: trigonometric arguments with |x| >= 2^45 return NaN (documented in DESIGN.md).
  */
 #ifndef RT_MATH_H
