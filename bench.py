@@ -32,7 +32,7 @@ RE = 6.3712e6
 # Algorithmic FP64 work per Haselgrove RHS evaluation: executed
 # DADD + DMUL + 2*DFMA per RHS of the minimal faithful schedule, calibrated once with ncu
 # (profiles/r1_flop_calibration.md) and frozen.
-FLOP_PER_RHS = {"cfg3": 2900.0, "cfg2": 2700.0}
+FLOP_PER_RHS = {"cfg3": 2602.0, "cfg2": 2307.0}
 
 
 def parse():
