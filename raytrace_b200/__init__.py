@@ -3,4 +3,4 @@ import os as _os
 
 __path__.insert(0, _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "ray-trace_b200"))
 from .api import *  # noqa: E402,F401,F403
-from . import api, build, multi, sweeps  # noqa: E402,F401
+from . import api, build, sweeps  # noqa: E402,F401
