@@ -13,7 +13,9 @@
 //     launch runs on full warps again (periodic stream compaction);
 //   * the seven stage derivatives live in shared memory as k[stage][component][thread] (conflict-free,
 //     one 8-byte word per lane), which lets the stage loop stay rolled: the RHS is instantiated once;
-//   * warps leave the attempt loop as soon as no lane is running (__any_sync vote).
+//   * warps leave the attempt loop as soon as no lane is running (__any_sync vote);
+//   * the work-list length is read from device memory, so slices are enqueued back to back without a host
+//     round trip; the host reads the counter once per batch of slices to shrink the grid and detect the end.
 #pragma once
 #include "rt_physics.cuh"
 
@@ -70,21 +72,23 @@ __device__ __forceinline__ void rt_dense_weights(double th, double *b) {
   b[6] = ((2.5 * (th - 1.0)) * (th - 0.6)) * th2;
 }
 
-template <int MODE>
+template <int MODE, bool COOP = false>
 __device__ __forceinline__ void rt_rhs(const RtDevEnv &E, const double *y, double par, double *dy, RtExtras2D *ex) {
   if (MODE == RT_PRESET_RAY3D)
-    rt_haselgrove_3d(E, y, par, dy);
+    rt_haselgrove_3d<COOP>(E, y, par, dy);
   else
-    rt_haselgrove_2d<MODE>(E, y, dy, ex);
+    rt_haselgrove_2d<MODE, COOP>(E, y, dy, ex);
 }
 
 // one trajectory row: (t, u[0..DIM)) and, in 2D, the save_func columns (RayTrace_lat.jl:318-324)
 template <int MODE>
 __device__ __forceinline__ void rt_traj_push(const RtState &S, const RtDevOpts &O, long long i, int &cnt, double t,
-                                             const double *u, const RtExtras2D &ex) {
+                                             const double *u, const RtExtras2D &ex, bool writer = true) {
   constexpr int DIM = RtTraits<MODE>::DIM, NCOL = RtTraits<MODE>::NCOL;
   if (cnt >= O.max_samples) return;
-  double *row = S.traj + ((size_t)i * (size_t)O.max_samples + (size_t)cnt) * NCOL;
+  cnt++;
+  if (!writer) return;
+  double *row = S.traj + ((size_t)i * (size_t)O.max_samples + (size_t)(cnt - 1)) * NCOL;
   row[0] = t;
 #pragma unroll
   for (int c = 0; c < DIM; c++) row[1 + c] = u[c];
@@ -94,7 +98,6 @@ __device__ __forceinline__ void rt_traj_push(const RtState &S, const RtDevOpts &
     row[7] = ex.dip;
     row[8] = ex.psi;
   }
-  cnt++;
 }
 
 // x^p through exp(p log x), out of line: three call sites per attempt would otherwise inline exp+log each
@@ -226,14 +229,23 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(RtDevEnv E, RtDevOpts
 }
 
 // ---- the slice kernel -----------------------------------------------------------------------------
-template <int MODE>
+template <int MODE, bool COOP>
 __global__ void __launch_bounds__(RT_BLOCK)
-    rt_integrate_kernel(RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in, int nactive,
-                        int *idx_out, int *count_out, int attempts) {
+    rt_integrate_kernel(RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in,
+                        const int *__restrict__ count_in, int *idx_out, int *count_out, int *count_clear,
+                        int attempts) {
   constexpr int DIM = RtTraits<MODE>::DIM;
   extern __shared__ double rt_smem[];
 #define RT_K(s, c) rt_smem[((s) * DIM + (c)) * RT_BLOCK + threadIdx.x]
-  const int j = blockIdx.x * RT_BLOCK + threadIdx.x;
+  // The work-list length lives in device memory (written by the previous launch), so the host can enqueue a
+  // batch of slices without synchronising; blocks beyond the list exit at once.  Three counters rotate:
+  // this launch reads count_in, appends to count_out and clears the one the next launch will append to.
+  const int nactive = *count_in;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *count_clear = 0;
+  constexpr int RAYS_PER_BLOCK = COOP ? RT_BLOCK / 8 : RT_BLOCK;  // COOP: 8 lanes share one ray (rt_physics.cuh)
+  if (blockIdx.x * RAYS_PER_BLOCK >= nactive) return;
+  const int j = blockIdx.x * RAYS_PER_BLOCK + (COOP ? (threadIdx.x >> 3) : threadIdx.x);
+  const bool writer = !COOP || (threadIdx.x & 7) == 0;
   const bool valid = j < nactive;
   const long long i = valid ? idx_in[j] : 0;
   const size_t n = (size_t)S.n;
@@ -284,7 +296,7 @@ __global__ void __launch_bounds__(RT_BLOCK)
         y[c] = u[c] + h * acc;
       }
       double dy[DIM];
-      rt_rhs<MODE>(E, y, par, dy, &ex);
+      rt_rhs<MODE, COOP>(E, y, par, dy, &ex);
 #pragma unroll
       for (int c = 0; c < DIM; c++) RT_K(s + 1, c) = dy[c];
     }
@@ -369,7 +381,7 @@ __global__ void __launch_bounds__(RT_BLOCK)
           if (MODE != RT_PRESET_RAY3D) {
             rt_extras_at<(MODE == RT_PRESET_RAY3D) ? RT_PRESET_LAT2D : MODE>(E, u, &ex);
           }
-          rt_traj_push<MODE>(S, O, i, cnt, t, u, ex);
+          rt_traj_push<MODE>(S, O, i, cnt, t, u, ex, writer);
         }
         continue;
       }
@@ -386,13 +398,13 @@ __global__ void __launch_bounds__(RT_BLOCK)
     const bool escaped = (O.r_esc > 0.0 && u[0] > O.r_esc);
     if (O.save_mode) {
       bool last = (t >= O.t1) || escaped;
-      if ((naccept % O.save_stride) == 0 || last) rt_traj_push<MODE>(S, O, i, cnt, t, u, ex);
+      if ((naccept % O.save_stride) == 0 || last) rt_traj_push<MODE>(S, O, i, cnt, t, u, ex, writer);
     }
     if (escaped) { status = RT_ESCAPED; running = false; continue; }
     h = hnew;
   }
 
-  if (valid) {
+  if (valid && writer) {
 #pragma unroll
     for (int c = 0; c < DIM; c++) {
       S.u[c * n + i] = u[c];
@@ -409,6 +421,6 @@ __global__ void __launch_bounds__(RT_BLOCK)
     S.nsamp[i] = cnt;
     S.status[i] = status;
   }
-  rt_enqueue(running, (int)i, idx_out, count_out);
+  rt_enqueue(running && writer, (int)i, idx_out, count_out);
 #undef RT_K
 }

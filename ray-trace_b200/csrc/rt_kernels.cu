@@ -217,7 +217,7 @@ extern "C" int rt_create(rt_ctx **out, int device) {
   ctx->stream = ctx->own_stream;
   for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&ctx->ev[k]));
   RT_CUDA(ctx, cudaMallocHost(&ctx->h_count, sizeof(int)));
-  RT_CUDA(ctx, cudaMalloc(&ctx->count, sizeof(int)));
+  RT_CUDA(ctx, cudaMalloc(&ctx->count, 4 * sizeof(int)));
   rt_env_preset(RT_PRESET_LAT2D, &ctx->env);
   rt_solver_preset(RT_PRESET_LAT2D, &ctx->opts);
   make_dev_env(ctx->env, ctx->denv);
@@ -499,28 +499,52 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   S.traj = ctx->traj;
   cudaStream_t st = ctx->stream;
   const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
-  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 128;
+  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // below this many live rays the GPU cannot be filled with one thread per ray: switch to 8 lanes per ray
+  const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
+  int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 8;
   ctx->stats = rt_stats{};
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
-  RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, sizeof(int), st));
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, 3 * sizeof(int), st));
   int cur = 0;
   rt_init_kernel<MODE><<<grid_for(n, RT_BLOCK), RT_BLOCK, 0, st>>>(ctx->denv, O, S, L, ctx->idx[cur], ctx->count);
   RT_CUDA(ctx, cudaGetLastError());
   ctx->stats.kernel_launches++;
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
+  // Slices are enqueued in batches with no host round trip in between: launch k reads count[k%3], appends to
+  // count[(k+1)%3] and clears count[(k+2)%3].  After each batch the host reads the live count to size the
+  // next batch's grid (an upper bound: the list only shrinks) and to stop.
+  long long upper = n;
+  int k = 0;
+  const int batch = 8;
   for (;;) {
-    RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count, ctx->count, sizeof(int), cudaMemcpyDeviceToHost, st));
-    RT_CUDA(ctx, cudaStreamSynchronize(st));
-    int nactive = *ctx->h_count;
-    if (nactive <= 0) break;
-    RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, sizeof(int), st));
-    rt_integrate_kernel<MODE><<<grid_for(nactive, RT_BLOCK), RT_BLOCK, smem, st>>>(
-        ctx->denv, O, S, ctx->idx[cur], nactive, ctx->idx[cur ^ 1], ctx->count, attempts);
+    const bool coop = upper <= coop_threshold;
+    for (int b = 0; b < batch; b++, k++) {
+      if (coop)
+        rt_integrate_kernel<MODE, true><<<grid_for(upper * 8, RT_BLOCK), RT_BLOCK, smem, st>>>(
+            ctx->denv, O, S, ctx->idx[cur], ctx->count + (k % 3), ctx->idx[cur ^ 1], ctx->count + ((k + 1) % 3),
+            ctx->count + ((k + 2) % 3), attempts);
+      else
+        rt_integrate_kernel<MODE, false><<<grid_for(upper, RT_BLOCK), RT_BLOCK, smem, st>>>(
+            ctx->denv, O, S, ctx->idx[cur], ctx->count + (k % 3), ctx->idx[cur ^ 1], ctx->count + ((k + 1) % 3),
+            ctx->count + ((k + 2) % 3), attempts);
+      cur ^= 1;
+      ctx->stats.kernel_launches++;
+      ctx->stats.slices++;
+    }
     RT_CUDA(ctx, cudaGetLastError());
-    cur ^= 1;
-    ctx->stats.kernel_launches++;
-    ctx->stats.slices++;
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count, ctx->count + (k % 3), sizeof(int), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(ctx, cudaStreamSynchronize(st));
+    upper = *ctx->h_count;
+    if (getenv("RT_DEBUG")) {
+      float ms = 0;
+      cudaEventRecord(ctx->ev[2], st);
+      cudaEventSynchronize(ctx->ev[2]);
+      cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]);
+      fprintf(stderr, "[rt] after %d slices (%d attempts): active=%lld t=%.2f ms\n", k, k * attempts, upper, ms);
+    }
+    if (upper <= 0) break;
   }
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
   rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, R.u_end + (size_t)(DIM - 1) * n, ctx->par,

@@ -39,7 +39,7 @@ class SolverOpts(C.Structure):
         ("dtmin", C.c_double),
         ("r_esc", C.c_double),
         ("slice_attempts", C.c_int32),
-        ("reserved", C.c_int32),
+        ("coop_threshold", C.c_int32),
     ]
 
 

@@ -100,10 +100,11 @@ def _check_solve(res, ref, rtol):
     assert _same(res.u_end, ref["u_end"]) and _same(res.t_end, ref["t_end"])
 
 
-def test_solve_2d_fixed_step_bitexact():
+@pytest.mark.parametrize("coop", [-1, 0])
+def test_solve_2d_fixed_step_bitexact(coop):
     launch = sweeps.sweep_2d(16, 8)
     rt = R.RayTracer("lat2d")
-    rt.set_solver(adaptive=0, dt=2.0e5, t1=6.0e7, maxiters=100000)
+    rt.set_solver(adaptive=0, dt=2.0e5, t1=6.0e7, maxiters=100000, coop_threshold=coop)
     res = rt.solve(launch)
     ref = O.solve_batch(O.env(O.LAT2D), O.opts(adaptive=0, dt=2.0e5, t1=6.0e7), launch, False, 8)
     _check_solve(res, ref, 1e-10)
@@ -113,14 +114,17 @@ def test_solve_2d_fixed_step_bitexact():
     rt.close()
 
 
+# coop_threshold: -1 = one thread per ray throughout; 0 = default (these small batches then run entirely with 8 lanes
+# per ray); 150 = switch from one mode to the other in the middle of the solve
+@pytest.mark.parametrize("coop", [-1, 0, 150])
 @pytest.mark.parametrize("name,pid", PRESETS_2D)
-def test_solve_2d_adaptive_bitexact(name, pid):
+def test_solve_2d_adaptive_bitexact(name, pid, coop):
     launch = sweeps.sweep_2d(24, 12)
     if pid != O.LAT2D:
         launch[1] = np.pi / 2 - launch[1]  # colatitude presets
     rt = R.RayTracer(name)
     rt.set_solver(adaptive=1, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, t1=4.0e8, maxiters=3000, r_esc=10 * RE,
-                  slice_attempts=37)
+                  slice_attempts=37, coop_threshold=coop)
     res = rt.solve(launch)
     ref = O.solve_batch(O.env(pid), O.opts(t1=4.0e8, maxiters=3000, r_esc=10 * RE), launch, False, 8)
     _check_solve(res, ref, 1e-7)
@@ -128,11 +132,12 @@ def test_solve_2d_adaptive_bitexact(name, pid):
     rt.close()
 
 
-def test_solve_3d_adaptive_bitexact_and_statuses():
+@pytest.mark.parametrize("coop", [-1, 0, 150])
+def test_solve_3d_adaptive_bitexact_and_statuses(coop):
     launch = sweeps.sweep_3d(8, 4, 10)
     launch[5, :3] = 0.0  # DtNaN rays (rho_phi = 0)
     rt = R.RayTracer("ray3d")
-    rt.set_solver(maxiters=5000, r_esc=10 * RE, slice_attempts=16)
+    rt.set_solver(maxiters=5000, r_esc=10 * RE, slice_attempts=16, coop_threshold=coop)
     res = rt.solve(launch)
     ref = O.solve_batch(O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, maxiters=5000, r_esc=10 * RE), launch, True, 8)
     _check_solve(res, ref, 1e-7)
@@ -141,10 +146,11 @@ def test_solve_3d_adaptive_bitexact_and_statuses():
     rt.close()
 
 
-def test_trajectories_match_oracle_2d():
+@pytest.mark.parametrize("coop", [-1, 0])
+def test_trajectories_match_oracle_2d(coop):
     launch = sweeps.sweep_2d(4, 3)
     rt = R.RayTracer("lat2d")
-    rt.set_solver(t1=3.0e8, save_mode=1, max_samples=512, save_stride=1)
+    rt.set_solver(t1=3.0e8, save_mode=1, max_samples=512, save_stride=1, coop_threshold=coop)
     res = rt.solve(launch)
     E, o = O.env(O.LAT2D), O.opts(t1=3.0e8, save_mode=1, max_samples=512)
     for k in range(launch.shape[1]):
@@ -153,10 +159,11 @@ def test_trajectories_match_oracle_2d():
     rt.close()
 
 
-def test_trajectories_match_oracle_3d_with_stride():
+@pytest.mark.parametrize("coop", [-1, 0])
+def test_trajectories_match_oracle_3d_with_stride(coop):
     launch = sweeps.sweep_3d(2, 2, 4)
     rt = R.RayTracer("ray3d")
-    rt.set_solver(save_mode=1, max_samples=64, save_stride=3)
+    rt.set_solver(save_mode=1, max_samples=64, save_stride=3, coop_threshold=coop)
     res = rt.solve(launch)
     E, o = O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, save_mode=1, max_samples=64, save_stride=3)
     for k in range(launch.shape[1]):

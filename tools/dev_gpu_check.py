@@ -38,7 +38,7 @@ if __name__ == "__main__":
     if "cfg3" in which:
         run("cfg3", "ray3d", sweeps.sweep_3d(), r_esc=10 * RE)
     if "cfg3slices" in which:
-        for sl in (8, 16, 32, 64, 256):
+        for sl in (2, 4, 8, 16, 32):
             run(f"cfg3 slice={sl}", "ray3d", sweeps.sweep_3d(), r_esc=10 * RE, slice_attempts=sl)
     if "cfg3prof" in which:
         run("cfg3-200k", "ray3d", sweeps.sweep_3d(20, 100, 100), r_esc=10 * RE)
