@@ -171,6 +171,17 @@ RT_API int rt_get_stats(const rt_ctx *ctx, rt_stats *stats);
 /* dependent-free DFMA throughput of this device in FLOP/s (roofline denominator) */
 RT_API int rt_measure_fp64_peak(rt_ctx *ctx, double *flops_per_s);
 
+
+/* ---- self-test hooks (diagnostics; not part of the reference-facing surface) ---------------------------- */
+/* Bit-equality of the kernels' branch-free division / sqrt / elementary functions against the exact ones on
+ * pseudo-random operands.  counts[10][3] = {compared, mismatches, flagged-to-exact-path} for
+ * div, div(shared rcp), div(constant divisor), sqrt, exp, 10^x, sincos, acos, atan, x^-4.5. */
+RT_API int rt_selftest_fastmath(int device, long long per_thread, unsigned long long seed,
+                                unsigned long long *counts, int ncounts);
+/* cycles per dependent operation with `warps` warps resident on one SM:
+ * res[6] = DFMA, DMUL, DADD, MUFU.RCP64H chains, then 2 and 4 independent DFMA chains per thread */
+RT_API int rt_probe_latency(int device, int warps, double *res);
+
 #ifdef __cplusplus
 }
 #endif

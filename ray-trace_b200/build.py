@@ -6,11 +6,11 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libraytrace_b200.so")
-SOURCES = ["rt_kernels.cu"]
-HEADERS = ["rt_math.h", "rt_physics.cuh", "rt_integrate.cuh", os.path.join("..", "..", "include", "raytrace_b200.h")]
+SOURCES = ["rt_kernels.cu", "rt_selftest.cu"]
+HEADERS = ["rt_math.h", "rt_fast.cuh", "rt_physics.cuh", "rt_integrate.cuh", os.path.join("..", "..", "include", "raytrace_b200.h")]
 
 NVCC_FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-t", "0", "-lineinfo", "-std=c++17",
     "-fmad=false",  # contraction off: fused multiply-adds exist only where rt_math.h writes them
     "-shared", "-Xcompiler", "-fPIC,-ffp-contract=off,-mfma,-fvisibility=hidden",
 ]
