@@ -5,7 +5,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libraytrace_b200.so")
+LIB = os.environ.get("RT_LIB") or os.path.join(HERE, "libraytrace_b200.so")  # RT_LIB: developer override (variant builds)
 SOURCES = ["rt_kernels.cu", "rt_selftest.cu"]
 HEADERS = ["rt_math.h", "rt_fast.cuh", "rt_physics.cuh", "rt_integrate.cuh", os.path.join("..", "..", "include", "raytrace_b200.h")]
 
@@ -28,7 +28,7 @@ def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [nvcc] + NVCC_FLAGS + os.environ.get("RT_EXTRA_FLAGS", "").split() + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)

@@ -17,9 +17,12 @@
 //   * the work-list length is read from device memory, so slices are enqueued back to back without a host
 //     round trip; the host reads the counter once per batch of slices to shrink the grid and detect the end.
 #pragma once
-#include "rt_physics.cuh"
+#include "rt_physics_fast.cuh"
 
 #define RT_BLOCK 128
+#ifndef RT_MINBLOCKS
+#define RT_MINBLOCKS 3  // __launch_bounds__ second argument for the integrate kernels (register budget)
+#endif
 
 struct RtDevOpts {
   int adaptive, save_mode, max_samples, save_stride;
@@ -72,12 +75,55 @@ __device__ __forceinline__ void rt_dense_weights(double th, double *b) {
   b[6] = ((2.5 * (th - 1.0)) * (th - 0.6)) * th2;
 }
 
+// ---- the right-hand side as the kernels call it -----------------------------------------------------
+// Fast path: the branch-free stream of rt_physics_fast.cuh.  When its flag comes back false (non-finite trial
+// stage, pole, zero numerator, argument outside a fast domain) the lane re-evaluates with the exact, branching
+// code of rt_physics.cuh, out of line.  Both produce the same bits wherever the fast path vouches for itself
+// (tests/test_gpu_parity.py compares against the CPU oracle, which only has the exact code).
+struct RtVec7 { double v[7]; };
+struct RtVec4x { double v[4]; RtExtras2D ex; };
+
+template <bool COOP>
+__device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 y, double par) {
+  RtVec7 d;
+  rt_haselgrove_3d<COOP>(*E, y.v, par, d.v);
+  return d;
+}
+template <int PRESET, bool COOP>
+__device__ __noinline__ RtVec4x rt_haselgrove_2d_exact(const RtDevEnv *E, RtVec4x y) {
+  RtVec4x d;
+  rt_haselgrove_2d<PRESET, COOP>(*E, y.v, d.v, &d.ex);
+  return d;
+}
+
+#ifndef RT_FORCE_EXACT
+#define RT_FORCE_EXACT 0
+#endif
+
 template <int MODE, bool COOP = false>
 __device__ __forceinline__ void rt_rhs(const RtDevEnv &E, const double *y, double par, double *dy, RtExtras2D *ex) {
-  if (MODE == RT_PRESET_RAY3D)
-    rt_haselgrove_3d<COOP>(E, y, par, dy);
-  else
+  if (MODE == RT_PRESET_RAY3D) {
+    if (RT_FORCE_EXACT || !rtf_haselgrove_3d<COOP>(E, y, par, dy)) {
+      RtVec7 in;
+#pragma unroll
+      for (int c = 0; c < 7; c++) in.v[c] = y[c];
+      RtVec7 out = rt_haselgrove_3d_exact<COOP>(&E, in, par);
+#pragma unroll
+      for (int c = 0; c < 7; c++) dy[c] = out.v[c];
+    }
+  } else if (MODE == RT_PRESET_LAT2D) {
+    if (RT_FORCE_EXACT || !rtf_haselgrove_2d_lat<COOP>(E, y, dy, ex)) {
+      RtVec4x in;
+#pragma unroll
+      for (int c = 0; c < 4; c++) in.v[c] = y[c];
+      RtVec4x out = rt_haselgrove_2d_exact<RT_PRESET_LAT2D, COOP>(&E, in);
+#pragma unroll
+      for (int c = 0; c < 4; c++) dy[c] = out.v[c];
+      if (ex) *ex = out.ex;
+    }
+  } else {
     rt_haselgrove_2d<MODE, COOP>(E, y, dy, ex);
+  }
 }
 
 // one trajectory row: (t, u[0..DIM)) and, in 2D, the save_func columns (RayTrace_lat.jl:318-324)
@@ -144,7 +190,7 @@ struct RtLaunch {
 };
 
 template <int MODE>
-__global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(RtDevEnv E, RtDevOpts O, RtState S, RtLaunch L,
+__global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(const __grid_constant__ RtDevEnv E, RtDevOpts O, RtState S, RtLaunch L,
                                                            int *idx_out, int *count_out) {
   constexpr int DIM = RtTraits<MODE>::DIM;
   long long i = (long long)blockIdx.x * RT_BLOCK + threadIdx.x;
@@ -230,8 +276,8 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(RtDevEnv E, RtDevOpts
 
 // ---- the slice kernel -----------------------------------------------------------------------------
 template <int MODE, bool COOP>
-__global__ void __launch_bounds__(RT_BLOCK)
-    rt_integrate_kernel(RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in,
+__global__ void __launch_bounds__(RT_BLOCK, RT_MINBLOCKS)
+    rt_integrate_kernel(const __grid_constant__ RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in,
                         const int *__restrict__ count_in, int *idx_out, int *count_out, int *count_clear,
                         int attempts) {
   constexpr int DIM = RtTraits<MODE>::DIM;

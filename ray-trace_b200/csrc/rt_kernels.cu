@@ -154,6 +154,20 @@ extern "C" int rt_solver_preset(int preset, rt_solver_opts *o) {
   return RT_OK;
 }
 
+// refined reciprocals of the constant divisors, with the division's own Newton sequence (rt_fast.cuh)
+__global__ void rt_env_rcp_kernel(RtDevEnv E, double *out) {
+  out[0] = rtf_rcp(E.re);
+  out[1] = rtf_rcp(E.eps_me);
+  out[2] = rtf_rcp(E.eps_mp);
+  out[3] = rtf_rcp(E.me);
+  out[4] = rtf_rcp(E.mp);
+  out[5] = rtf_rcp(1.5);
+  out[6] = rtf_rcp(10.0);
+  out[7] = rtf_rcp(0.1);
+  out[8] = rtf_rcp(1.0e-11);
+  out[9] = rtf_rcp(1.0e-5);
+}
+
 static void make_dev_env(const rt_env_params &e, RtDevEnv &d) {
   d.c = e.c;
   d.re = e.re;
@@ -173,6 +187,22 @@ static void make_dev_env(const rt_env_params &e, RtDevEnv &d) {
   d.iono_n0 = e.iono_n0;
   d.iono_k = e.iono_k;
   d.iono_h = e.iono_h;
+  d.inv_c = 1.0 / e.c;
+}
+
+static int refresh_rcp(rt_ctx *ctx) {
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  double *d = nullptr, h[10];
+  RT_CUDA(ctx, cudaMalloc(&d, sizeof(h)));
+  rt_env_rcp_kernel<<<1, 1, 0, ctx->stream>>>(ctx->denv, d);
+  cudaError_t e = cudaMemcpyAsync(h, d, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) return set_err(ctx, RT_ERR_CUDA, "refresh_rcp: %s", cudaGetErrorString(e));
+  RtDevEnv &v = ctx->denv;
+  v.y_re = h[0]; v.y_eps_me = h[1]; v.y_eps_mp = h[2]; v.y_me = h[3]; v.y_mp = h[4];
+  v.y_1p5 = h[5]; v.y_10 = h[6]; v.y_0p1 = h[7]; v.y_dth = h[8]; v.y_df = h[9];
+  return RT_OK;
 }
 
 static RtDevOpts make_dev_opts(const rt_solver_opts &o) {
@@ -221,6 +251,11 @@ extern "C" int rt_create(rt_ctx **out, int device) {
   rt_env_preset(RT_PRESET_LAT2D, &ctx->env);
   rt_solver_preset(RT_PRESET_LAT2D, &ctx->opts);
   make_dev_env(ctx->env, ctx->denv);
+  if (int rc = refresh_rcp(ctx)) {
+    g_last_error = ctx->err;
+    rt_destroy(ctx);
+    return rc;
+  }
   *out = ctx;
   return RT_OK;
 }
@@ -261,7 +296,7 @@ extern "C" int rt_set_env(rt_ctx *ctx, const rt_env_params *env) {
   if (env->preset < 0 || env->preset > 3) return set_err(ctx, RT_ERR_INVALID, "rt_set_env: bad preset %d", env->preset);
   ctx->env = *env;
   make_dev_env(ctx->env, ctx->denv);
-  return RT_OK;
+  return refresh_rcp(ctx);
 }
 
 extern "C" int rt_set_solver(rt_ctx *ctx, const rt_solver_opts *o) {
@@ -309,7 +344,7 @@ static int ensure_stage(rt_ctx *ctx, size_t dbytes, size_t ibytes) {
 // Batch pointwise evaluators
 // ---------------------------------------------------------------------------------------------------
 template <int MODE>
-__global__ void rt_mu2d_kernel(RtDevEnv E, long long n, const double *r, const double *th, const double *chi,
+__global__ void rt_mu2d_kernel(const __grid_constant__ RtDevEnv E, long long n, const double *r, const double *th, const double *chi,
                                const double *f, double *mu, double *dmu) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -318,7 +353,7 @@ __global__ void rt_mu2d_kernel(RtDevEnv E, long long n, const double *r, const d
   dmu[i] = m.dmudpsi;
 }
 
-__global__ void rt_mu3d_kernel(RtDevEnv E, long long n, const double *in /*[7][n]*/, double *out /*[6][n]*/) {
+__global__ void rt_mu3d_kernel(const __grid_constant__ RtDevEnv E, long long n, const double *in /*[7][n]*/, double *out /*[6][n]*/) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   RtGeo3D g;
@@ -333,7 +368,7 @@ __global__ void rt_mu3d_kernel(RtDevEnv E, long long n, const double *in /*[7][n
 }
 
 template <int MODE>
-__global__ void rt_rhs_kernel(RtDevEnv E, long long n, const double *u, const double *freq, double *du) {
+__global__ void rt_rhs_kernel(const __grid_constant__ RtDevEnv E, long long n, const double *u, const double *freq, double *du) {
   constexpr int DIM = RtTraits<MODE>::DIM;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;

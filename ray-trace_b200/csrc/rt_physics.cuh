@@ -28,6 +28,10 @@ struct RtDevEnv {
   double eps_mp;   // eps*mp
   double Lppi, Lppo, ne_Lppi, ca_coef, ca_trough;
   double iono_n0, iono_k, iono_h;
+  // for the branch-free path (rt_physics_fast.cuh): refined reciprocals of the constant divisors, produced on the
+  // device by rt_env_rcp_kernel with the division's own Newton sequence, and 1/c (an IEEE quotient, host-computed)
+  double y_re, y_eps_me, y_eps_mp, y_me, y_mp, y_1p5, y_10, y_0p1, y_dth, y_df;
+  double inv_c;
 };
 
 struct RtPlasma {  // local medium at one point (independent of wave frequency)
