@@ -178,6 +178,9 @@ RT_API int rt_measure_fp64_peak(rt_ctx *ctx, double *flops_per_s);
  * div, div(shared rcp), div(constant divisor), sqrt, exp, 10^x, sincos, acos, atan, x^-4.5. */
 RT_API int rt_selftest_fastmath(int device, long long per_thread, unsigned long long seed,
                                 unsigned long long *counts, int ncounts);
+/* how often the kernels left the branch-free right-hand side for the exact one since the last reset:
+ * out8 = {calls, r out of range, non-finite input, non-finite result, finite both (conservative guard), 2D calls, 0, 0} */
+RT_API int rt_debug_fallback_counts(rt_ctx *ctx, unsigned long long *out8, int reset);
 /* cycles per dependent operation with `warps` warps resident on one SM:
  * res[6] = DFMA, DMUL, DADD, MUFU.RCP64H chains, then 2 and 4 independent DFMA chains per thread */
 RT_API int rt_probe_latency(int device, int warps, double *res);

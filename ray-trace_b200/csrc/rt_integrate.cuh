@@ -83,16 +83,32 @@ __device__ __forceinline__ void rt_dense_weights(double th, double *b) {
 struct RtVec7 { double v[7]; };
 struct RtVec4x { double v[4]; RtExtras2D ex; };
 
+// fallback census (cold path only): [0] calls, [1] r < 2^16 or negative, [2] non-finite input, [3] non-finite result,
+// [4] finite in and out (a guard was merely conservative), [5] 2D calls
+__device__ unsigned long long rt_dbg_fallback[8];
+
 template <bool COOP>
 __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 y, double par) {
   RtVec7 d;
   rt_haselgrove_3d<COOP>(*E, y.v, par, d.v);
+  bool fin_in = true, fin_out = true;
+#pragma unroll
+  for (int c = 0; c < 7; c++) {
+    fin_in = fin_in && rt_isfinite(y.v[c]);
+    fin_out = fin_out && rt_isfinite(d.v[c]);
+  }
+  atomicAdd(&rt_dbg_fallback[0], 1ULL);
+  if (!(y.v[0] >= 65536.0)) atomicAdd(&rt_dbg_fallback[1], 1ULL);
+  else if (!fin_in) atomicAdd(&rt_dbg_fallback[2], 1ULL);
+  else if (!fin_out) atomicAdd(&rt_dbg_fallback[3], 1ULL);
+  else atomicAdd(&rt_dbg_fallback[4], 1ULL);
   return d;
 }
 template <int PRESET, bool COOP>
 __device__ __noinline__ RtVec4x rt_haselgrove_2d_exact(const RtDevEnv *E, RtVec4x y) {
   RtVec4x d;
   rt_haselgrove_2d<PRESET, COOP>(*E, y.v, d.v, &d.ex);
+  atomicAdd(&rt_dbg_fallback[5], 1ULL);
   return d;
 }
 

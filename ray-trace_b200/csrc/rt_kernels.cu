@@ -754,6 +754,18 @@ extern "C" int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples) {
   return RT_OK;
 }
 
+// census of exact-path fallbacks since the last reset (diagnostics)
+extern "C" int rt_debug_fallback_counts(rt_ctx *ctx, unsigned long long *out8, int reset) {
+  if (!ctx || !out8) return set_err(ctx, RT_ERR_INVALID, "rt_debug_fallback_counts: null argument");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  RT_CUDA(ctx, cudaMemcpyFromSymbol(out8, rt_dbg_fallback, 8 * sizeof(unsigned long long)));
+  if (reset) {
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    RT_CUDA(ctx, cudaMemcpyToSymbol(rt_dbg_fallback, z, sizeof(z)));
+  }
+  return RT_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // FP64 roofline denominator: 8 independent DFMA chains per thread, all SMs full
 // ---------------------------------------------------------------------------------------------------

@@ -23,6 +23,10 @@ def run(name, preset, launch, **kw):
         print(f"{name} rep{rep}: n={launch.shape[1]} wall={wall:.3f}s total_ms={st.total_ms:.1f} integ_ms={st.integrate_ms:.1f} "
               f"slices={st.slices} nfe={nfe:.3e} rhs/s={nfe / (st.total_ms * 1e-3):.3e} rays/s={launch.shape[1] / (st.total_ms * 1e-3):.3e}",
               flush=True)
+    import ctypes as C
+    fb = (C.c_ulonglong * 8)()
+    R.api._lib().rt_debug_fallback_counts(rt._ctx, fb, 1)
+    print("   exact-path fallbacks:", list(fb), "of", nfe * 2, "RHS evaluations (2 reps)", flush=True)
     u, c = np.unique(res.status, return_counts=True)
     print("   status:", {R.STATUS_NAMES[int(a)]: int(b) for a, b in zip(u, c)}, "naccept min/med/max",
           res.naccept.min(), int(np.median(res.naccept)), res.naccept.max(), "nreject max", res.nreject.max(), flush=True)
