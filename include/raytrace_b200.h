@@ -83,6 +83,8 @@ typedef struct rt_solver_opts {
   double r_esc;          /* [EXT] escape radius in metres, <= 0 disables */
   int32_t slice_attempts;/* step attempts per kernel launch between compactions (0 = default 8) */
   int32_t coop_threshold;/* live-ray count at or below which 8 lanes share one ray (0 = default 10000, < 0 = never) */
+  int32_t single_chain;  /* 0 = rays that start upward run as a separate, prioritised chain of launches; 1 = one chain */
+  int32_t reserved;
 } rt_solver_opts;
 
 /* Caller-allocated structure-of-arrays result.  dim = 4 (2D) or 7 (3D). */
@@ -166,6 +168,7 @@ typedef struct rt_stats {
   double integrate_ms;       /* CUDA-event time of the integrate kernels of the last solve */
   double total_ms;           /* CUDA-event time of the whole last solve on the stream */
   int64_t total_nfe;         /* sum of nfe over rays of the last solve */
+  int64_t prio_rays;         /* rays the last solve put on the priority chain */
 } rt_stats;
 RT_API int rt_get_stats(const rt_ctx *ctx, rt_stats *stats);
 /* dependent-free DFMA throughput of this device in FLOP/s (roofline denominator) */

@@ -16,6 +16,7 @@ mutable struct SolverOpts   # rt_solver_opts
     adaptive::Int32; save_mode::Int32; max_samples::Int32; save_stride::Int32
     maxiters::Int64; t1::Float64; dt::Float64; reltol::Float64; abstol::Float64
     dtmax::Float64; dtmin::Float64; r_esc::Float64; slice_attempts::Int32; coop_threshold::Int32
+    single_chain::Int32; reserved::Int32
 end
 
 struct Result         # rt_result: caller-allocated arrays
@@ -60,7 +61,7 @@ end
 # (RayTrace_lat.jl:337-338).  launch columns r, θ, χ, f, t as in ray_start.dat (README.md:11).
 function solve_2d(ctx, r, θ, χ, f, t0; reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, tspan_end=5.0e9, maxiters=100_000)
     n = length(r)
-    o = SolverOpts(1, 0, 0, 1, maxiters, tspan_end, 0.0, reltol, abstol, dtmax, dtmin, 0.0, 0, 0)
+    o = SolverOpts(1, 0, 0, 1, maxiters, tspan_end, 0.0, reltol, abstol, dtmax, dtmin, 0.0, 0, 0, 0, 0)
     check(ccall((:rt_set_solver, LIB), Cint, (Ptr{Cvoid}, Ref{SolverOpts}), ctx, o), ctx)
     u_end = Matrix{Float64}(undef, n, 4); t_end = Vector{Float64}(undef, n); T = similar(t_end)
     ints = [Vector{Int32}(undef, n) for _ in 1:5]

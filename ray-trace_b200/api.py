@@ -44,7 +44,7 @@ class SolverOpts(C.Structure):
         ("adaptive", C.c_int32), ("save_mode", C.c_int32), ("max_samples", C.c_int32), ("save_stride", C.c_int32),
         ("maxiters", C.c_int64), ("t1", C.c_double), ("dt", C.c_double), ("reltol", C.c_double),
         ("abstol", C.c_double), ("dtmax", C.c_double), ("dtmin", C.c_double), ("r_esc", C.c_double),
-        ("slice_attempts", C.c_int32), ("coop_threshold", C.c_int32),
+        ("slice_attempts", C.c_int32), ("coop_threshold", C.c_int32), ("single_chain", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -54,7 +54,7 @@ class _Result(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_int64), ("slices", C.c_int64), ("integrate_ms", C.c_double),
-                ("total_ms", C.c_double), ("total_nfe", C.c_int64)]
+                ("total_ms", C.c_double), ("total_nfe", C.c_int64), ("prio_rays", C.c_int64)]
 
 
 _LIB = None

@@ -206,12 +206,18 @@ struct RtLaunch {
 };
 
 template <int MODE>
+// Rays are appended to one of two work lists.  List 1 ("priority") takes the rays that start upward
+// (dr/dt > 0 at launch): those are the ones that can travel to the conjugate hemisphere and need 10-40x the
+// steps of a ray that goes straight down, so the host starts them first, on their own stream, and the long
+// dependent chains overlap the bulk of the sweep instead of trailing it.  Scheduling only: results do not
+// depend on which list a ray is in.
 __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(const __grid_constant__ RtDevEnv E, RtDevOpts O, RtState S, RtLaunch L,
-                                                           int *idx_out, int *count_out) {
+                                                           int *idx_out, int *count_out, int *idx_prio,
+                                                           int *count_prio) {
   constexpr int DIM = RtTraits<MODE>::DIM;
   long long i = (long long)blockIdx.x * RT_BLOCK + threadIdx.x;
   bool valid = i < S.n;
-  bool running = false;
+  bool running = false, prio = false;
   if (valid) {
     double u[DIM], k1[DIM], y[DIM], f1[DIM], sk[DIM];
 #pragma unroll
@@ -286,8 +292,10 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(const __grid_constant
     if (O.save_mode) rt_traj_push<MODE>(S, O, i, cnt, t0, u, ex);
     S.nsamp[i] = cnt;
     running = (status == RT_RUNNING);
+    prio = (idx_prio != nullptr) && (k1[0] > 0.0);
   }
-  rt_enqueue(running, (int)i, idx_out, count_out);
+  rt_enqueue(running && !prio, (int)i, idx_out, count_out);
+  if (idx_prio != nullptr) rt_enqueue(running && prio, (int)i, idx_prio, count_prio);
 }
 
 // ---- the slice kernel -----------------------------------------------------------------------------

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <limits>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "rt_integrate.cuh"
@@ -30,6 +31,9 @@ struct rt_ctx {
   int cap_dim = 0;
   double *k1 = nullptr, *h = nullptr, *qold = nullptr, *par = nullptr;
   int *sgn = nullptr, *nsamp = nullptr, *idx[2] = {nullptr, nullptr}, *count = nullptr;
+  int *idx_prio[2] = {nullptr, nullptr};  // work lists of the priority chain (count + 4 .. count + 6 are its counters)
+  cudaStream_t prio_stream = nullptr;     // high-priority stream of the priority chain
+  cudaEvent_t ev_chain[2] = {nullptr, nullptr}, ev_fork = nullptr, ev_join = nullptr;
   double *traj = nullptr;
   size_t traj_bytes = 0;
   int *h_count = nullptr;  // pinned
@@ -246,8 +250,16 @@ extern "C" int rt_create(rt_ctx **out, int device) {
   RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
   ctx->stream = ctx->own_stream;
   for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&ctx->ev[k]));
-  RT_CUDA(ctx, cudaMallocHost(&ctx->h_count, sizeof(int)));
-  RT_CUDA(ctx, cudaMalloc(&ctx->count, 4 * sizeof(int)));
+  RT_CUDA(ctx, cudaMallocHost(&ctx->h_count, 4 * sizeof(int)));
+  RT_CUDA(ctx, cudaMalloc(&ctx->count, 8 * sizeof(int)));
+  {
+    int lo = 0, hi = 0;
+    RT_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    RT_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->prio_stream, cudaStreamNonBlocking, hi));
+    for (int k = 0; k < 2; k++) RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_chain[k], cudaEventDisableTiming));
+    RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+  }
   rt_env_preset(RT_PRESET_LAT2D, &ctx->env);
   rt_solver_preset(RT_PRESET_LAT2D, &ctx->opts);
   make_dev_env(ctx->env, ctx->denv);
@@ -269,6 +281,9 @@ static void free_work(rt_ctx *ctx) {
   cudaFree(ctx->nsamp);
   cudaFree(ctx->idx[0]);
   cudaFree(ctx->idx[1]);
+  cudaFree(ctx->idx_prio[0]);
+  cudaFree(ctx->idx_prio[1]);
+  ctx->idx_prio[0] = ctx->idx_prio[1] = nullptr;
   ctx->k1 = ctx->h = ctx->qold = ctx->par = nullptr;
   ctx->sgn = ctx->nsamp = ctx->idx[0] = ctx->idx[1] = nullptr;
   ctx->cap_rays = 0;
@@ -287,6 +302,11 @@ extern "C" void rt_destroy(rt_ctx *ctx) {
   cudaFreeHost(ctx->h_count);
   for (int k = 0; k < 4; k++)
     if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+  for (int k = 0; k < 2; k++)
+    if (ctx->ev_chain[k]) cudaEventDestroy(ctx->ev_chain[k]);
+  if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+  if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+  if (ctx->prio_stream) cudaStreamDestroy(ctx->prio_stream);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -491,6 +511,8 @@ static int ensure_work(rt_ctx *ctx, size_t n, int dim, const RtDevOpts &O, int n
     RT_CUDA(ctx, cudaMalloc(&ctx->nsamp, cap * sizeof(int)));
     RT_CUDA(ctx, cudaMalloc(&ctx->idx[0], cap * sizeof(int)));
     RT_CUDA(ctx, cudaMalloc(&ctx->idx[1], cap * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->idx_prio[0], cap * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->idx_prio[1], cap * sizeof(int)));
     ctx->cap_rays = cap;
     ctx->cap_dim = dim;
   }
@@ -536,50 +558,104 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // below this many live rays the GPU cannot be filled with one thread per ray: switch to 8 lanes per ray
+  // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 8 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
-  int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 8;
+  const int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 8;
+  const bool two_chains = ctx->opts.single_chain == 0;
   ctx->stats = rt_stats{};
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
-  RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, 3 * sizeof(int), st));
-  int cur = 0;
-  rt_init_kernel<MODE><<<grid_for(n, RT_BLOCK), RT_BLOCK, 0, st>>>(ctx->denv, O, S, L, ctx->idx[cur], ctx->count);
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, 8 * sizeof(int), st));
+  rt_init_kernel<MODE><<<grid_for(n, RT_BLOCK), RT_BLOCK, 0, st>>>(ctx->denv, O, S, L, ctx->idx[0], ctx->count,
+                                                                  two_chains ? ctx->idx_prio[0] : nullptr,
+                                                                  ctx->count + 4);
   RT_CUDA(ctx, cudaGetLastError());
   ctx->stats.kernel_launches++;
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
-  // Slices are enqueued in batches with no host round trip in between: launch k reads count[k%3], appends to
-  // count[(k+1)%3] and clears count[(k+2)%3].  After each batch the host reads the live count to size the
-  // next batch's grid (an upper bound: the list only shrinks) and to stop.
-  long long upper = n;
-  int k = 0;
-  const int batch = 8;
+  RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count, ctx->count, sizeof(int), cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count + 1, ctx->count + 4, sizeof(int), cudaMemcpyDeviceToHost, st));
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev_fork, st));
+  RT_CUDA(ctx, cudaStreamSynchronize(st));
+  // Two independent chains of slices: chain 0 (normal list) on the caller's stream, chain 1 (priority list:
+  // rays that start upward, see rt_init_kernel) on the context's high-priority stream.  Within a chain, launch k
+  // reads counter k%3, appends survivors to counter (k+1)%3 and clears (k+2)%3, so a batch of slices needs no
+  // host round trip; after each batch the host reads the live count (an upper bound for the next batch's grid:
+  // a list only shrinks).  The host polls the two chains' events and feeds whichever is idle.
+  struct Chain {
+    cudaStream_t st;
+    int *idx[2];
+    int *cnt;
+    int *h;
+    cudaEvent_t ev;
+    long long upper;
+    int cur, k;
+    bool pending;
+  } ch[2] = {{st, {ctx->idx[0], ctx->idx[1]}, ctx->count, ctx->h_count + 2, ctx->ev_chain[0], ctx->h_count[0], 0, 0, false},
+             {ctx->prio_stream, {ctx->idx_prio[0], ctx->idx_prio[1]}, ctx->count + 4, ctx->h_count + 3, ctx->ev_chain[1],
+              ctx->h_count[1], 0, 0, false}};
+  ctx->stats.prio_rays = ch[1].upper;
+  if (ch[1].upper > 0) RT_CUDA(ctx, cudaStreamWaitEvent(ch[1].st, ctx->ev_fork, 0));
+  const bool dbg = getenv("RT_DEBUG") != nullptr;
   for (;;) {
-    const bool coop = upper <= coop_threshold;
-    for (int b = 0; b < batch; b++, k++) {
-      if (coop)
-        rt_integrate_kernel<MODE, true><<<grid_for(upper * 8, RT_BLOCK), RT_BLOCK, smem, st>>>(
-            ctx->denv, O, S, ctx->idx[cur], ctx->count + (k % 3), ctx->idx[cur ^ 1], ctx->count + ((k + 1) % 3),
-            ctx->count + ((k + 2) % 3), attempts);
-      else
-        rt_integrate_kernel<MODE, false><<<grid_for(upper, RT_BLOCK), RT_BLOCK, smem, st>>>(
-            ctx->denv, O, S, ctx->idx[cur], ctx->count + (k % 3), ctx->idx[cur ^ 1], ctx->count + ((k + 1) % 3),
-            ctx->count + ((k + 2) % 3), attempts);
-      cur ^= 1;
-      ctx->stats.kernel_launches++;
-      ctx->stats.slices++;
+    bool any = false;
+    for (int c = 1; c >= 0; c--) {  // priority chain first
+      Chain &C = ch[c];
+      if (C.pending) {
+        cudaError_t q = cudaEventQuery(C.ev);
+        if (q == cudaSuccess) {
+          C.pending = false;
+          C.upper = *C.h;
+          if (dbg) {
+            float ms = 0;
+            cudaEventRecord(ctx->ev[2], C.st);
+            cudaEventSynchronize(ctx->ev[2]);
+            cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]);
+            fprintf(stderr, "[rt] chain %d after %d slices (%d attempts): active=%lld t=%.2f ms\n", c, C.k, C.k * attempts,
+                    C.upper, ms);
+          }
+        } else if (q != cudaErrorNotReady) {
+          return set_err(ctx, RT_ERR_CUDA, "integrate chain %d: %s", c, cudaGetErrorString(q));
+        }
+      }
+      if (!C.pending && C.upper > 0) {
+        // 8 lanes per ray buys latency with throughput (the five refractive-index evaluations run side by side,
+        // everything else is replicated): only worth it when the GPU has nothing else to do, i.e. when this
+        // chain is short AND the other chain is (all but) finished
+        const Chain &other = ch[c ^ 1];
+        const bool coop = C.upper <= coop_threshold && other.upper <= 2048;  // (a nearly finished chain leaves the GPU idle too)
+        const int batch = coop ? 16 : 8;
+        for (int b = 0; b < batch; b++, C.k++) {
+          const int k = C.k;
+          if (coop)
+            rt_integrate_kernel<MODE, true><<<grid_for(C.upper * 8, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
+                ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
+                C.cnt + ((k + 2) % 3), attempts);
+          else
+            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
+                ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
+                C.cnt + ((k + 2) % 3), attempts);
+          C.cur ^= 1;
+          ctx->stats.kernel_launches++;
+          ctx->stats.slices++;
+        }
+        RT_CUDA(ctx, cudaGetLastError());
+        RT_CUDA(ctx, cudaMemcpyAsync(C.h, C.cnt + (C.k % 3), sizeof(int), cudaMemcpyDeviceToHost, C.st));
+        RT_CUDA(ctx, cudaEventRecord(C.ev, C.st));
+        C.pending = true;
+      }
+      any = any || C.pending;
     }
-    RT_CUDA(ctx, cudaGetLastError());
-    RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count, ctx->count + (k % 3), sizeof(int), cudaMemcpyDeviceToHost, st));
-    RT_CUDA(ctx, cudaStreamSynchronize(st));
-    upper = *ctx->h_count;
-    if (getenv("RT_DEBUG")) {
-      float ms = 0;
-      cudaEventRecord(ctx->ev[2], st);
-      cudaEventSynchronize(ctx->ev[2]);
-      cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]);
-      fprintf(stderr, "[rt] after %d slices (%d attempts): active=%lld t=%.2f ms\n", k, k * attempts, upper, ms);
+    if (!any) break;
+    if (ch[0].pending && ch[1].pending) {  // both busy: block on the one that is ahead in the queue instead of spinning hot
+      std::this_thread::yield();
+    } else if (ch[0].pending && ch[1].upper <= 0) {
+      cudaEventSynchronize(ch[0].ev);
+    } else if (ch[1].pending && ch[0].upper <= 0) {
+      cudaEventSynchronize(ch[1].ev);
     }
-    if (upper <= 0) break;
+  }
+  if (ch[1].k > 0) {  // join the priority stream back into the caller's stream
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_join, ch[1].st));
+    RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_join, 0));
   }
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
   rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, R.u_end + (size_t)(DIM - 1) * n, ctx->par,

@@ -40,6 +40,8 @@ class SolverOpts(C.Structure):
         ("r_esc", C.c_double),
         ("slice_attempts", C.c_int32),
         ("coop_threshold", C.c_int32),
+        ("single_chain", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 
@@ -73,7 +75,7 @@ def env(preset=LAT2D):
 def opts(adaptive=1, t1=5.0e9, dt=0.0, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, maxiters=100000,
          r_esc=0.0, save_mode=0, max_samples=0, save_stride=1, slice_attempts=0):
     return SolverOpts(adaptive, save_mode, max_samples, save_stride, maxiters, t1, dt, reltol, abstol, dtmax,
-                      dtmin, r_esc, slice_attempts, 0)
+                      dtmin, r_esc, slice_attempts, 0, 0, 0)
 
 
 def _d(x):
