@@ -87,10 +87,9 @@ struct RtVec4x { double v[4]; RtExtras2D ex; };
 // [4] finite in and out (a guard was merely conservative), [5] 2D calls
 __device__ unsigned long long rt_dbg_fallback[8];
 
-template <bool COOP>
 __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 y, double par) {
   RtVec7 d;
-  rt_haselgrove_3d<COOP>(*E, y.v, par, d.v);
+  rt_haselgrove_3d(*E, y.v, par, d.v);
   bool fin_in = true, fin_out = true;
 #pragma unroll
   for (int c = 0; c < 7; c++) {
@@ -104,10 +103,10 @@ __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 
   else atomicAdd(&rt_dbg_fallback[4], 1ULL);
   return d;
 }
-template <int PRESET, bool COOP>
+template <int PRESET>
 __device__ __noinline__ RtVec4x rt_haselgrove_2d_exact(const RtDevEnv *E, RtVec4x y) {
   RtVec4x d;
-  rt_haselgrove_2d<PRESET, COOP>(*E, y.v, d.v, &d.ex);
+  rt_haselgrove_2d<PRESET>(*E, y.v, d.v, &d.ex);
   atomicAdd(&rt_dbg_fallback[5], 1ULL);
   return d;
 }
@@ -123,7 +122,7 @@ __device__ __forceinline__ void rt_rhs(const RtDevEnv &E, const double *y, doubl
       RtVec7 in;
 #pragma unroll
       for (int c = 0; c < 7; c++) in.v[c] = y[c];
-      RtVec7 out = rt_haselgrove_3d_exact<COOP>(&E, in, par);
+      RtVec7 out = rt_haselgrove_3d_exact(&E, in, par);  // (cooperative mode: every lane of the group, redundantly)
 #pragma unroll
       for (int c = 0; c < 7; c++) dy[c] = out.v[c];
     }
@@ -132,13 +131,13 @@ __device__ __forceinline__ void rt_rhs(const RtDevEnv &E, const double *y, doubl
       RtVec4x in;
 #pragma unroll
       for (int c = 0; c < 4; c++) in.v[c] = y[c];
-      RtVec4x out = rt_haselgrove_2d_exact<RT_PRESET_LAT2D, COOP>(&E, in);
+      RtVec4x out = rt_haselgrove_2d_exact<RT_PRESET_LAT2D>(&E, in);
 #pragma unroll
       for (int c = 0; c < 4; c++) dy[c] = out.v[c];
       if (ex) *ex = out.ex;
     }
   } else {
-    rt_haselgrove_2d<MODE, COOP>(E, y, dy, ex);
+    rt_haselgrove_2d<MODE>(E, y, dy, ex);  // RayMain / scratch variants: exact code only (replicated when cooperative)
   }
 }
 
@@ -300,7 +299,7 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(const __grid_constant
 
 // ---- the slice kernel -----------------------------------------------------------------------------
 template <int MODE, bool COOP>
-__global__ void __launch_bounds__(RT_BLOCK, RT_MINBLOCKS)
+__global__ void __launch_bounds__(RT_BLOCK, COOP ? 1 : RT_MINBLOCKS)  // COOP runs a few warps per SM: no register cap
     rt_integrate_kernel(const __grid_constant__ RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in,
                         const int *__restrict__ count_in, int *idx_out, int *count_out, int *count_clear,
                         int attempts) {
@@ -312,11 +311,14 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MINBLOCKS)
   // this launch reads count_in, appends to count_out and clears the one the next launch will append to.
   const int nactive = *count_in;
   if (blockIdx.x == 0 && threadIdx.x == 0) *count_clear = 0;
-  constexpr int RAYS_PER_BLOCK = COOP ? RT_BLOCK / 8 : RT_BLOCK;  // COOP: 8 lanes share one ray (rt_physics.cuh)
+  // COOP: 3 lanes share one ray, 10 rays per warp, lanes 30 and 31 idle (rt_physics.cuh)
+  constexpr int RAYS_PER_BLOCK = COOP ? (RT_BLOCK / 32) * RT_COOP_RAYS_PER_WARP : RT_BLOCK;
   if (blockIdx.x * RAYS_PER_BLOCK >= nactive) return;
-  const int j = blockIdx.x * RAYS_PER_BLOCK + (COOP ? (threadIdx.x >> 3) : threadIdx.x);
-  const bool writer = !COOP || (threadIdx.x & 7) == 0;
-  const bool valid = j < nactive;
+  const int lane = threadIdx.x & 31;
+  const int j = blockIdx.x * RAYS_PER_BLOCK +
+                (COOP ? (threadIdx.x >> 5) * RT_COOP_RAYS_PER_WARP + ((lane * 11) >> 5) : threadIdx.x);
+  const bool writer = !COOP || rt_group_rank() == 0;
+  const bool valid = j < nactive && (!COOP || lane < 3 * RT_COOP_RAYS_PER_WARP);
   const long long i = valid ? idx_in[j] : 0;
   const size_t n = (size_t)S.n;
 

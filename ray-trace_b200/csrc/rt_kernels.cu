@@ -558,7 +558,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 8 lanes per ray
+  // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
   const int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 8;
   const bool two_chains = ctx->opts.single_chain == 0;
@@ -609,7 +609,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
             cudaEventRecord(ctx->ev[2], C.st);
             cudaEventSynchronize(ctx->ev[2]);
             cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]);
-            fprintf(stderr, "[rt] chain %d after %d slices (%d attempts): active=%lld t=%.2f ms\n", c, C.k, C.k * attempts,
+            fprintf(stderr, "[rt] chain %d after %d slices (%d attempts): active=%lld t=%.2f ms\n", c, C.k, C.k * attempts /* nominal */,
                     C.upper, ms);
           }
         } else if (q != cudaErrorNotReady) {
@@ -617,22 +617,27 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         }
       }
       if (!C.pending && C.upper > 0) {
-        // 8 lanes per ray buys latency with throughput (the five refractive-index evaluations run side by side,
-        // everything else is replicated): only worth it when the GPU has nothing else to do, i.e. when this
-        // chain is short AND the other chain is (all but) finished
+        // 3 lanes per ray (rt_physics.cuh) buys latency (0.45x per right-hand side) with throughput (1.4x the issue
+        // slots): used once a chain is down to its long rays.  RT_COOP_POLICY=0 (developer switch) lifts the restriction to
+        // the time when the other chain is all but finished.
         const Chain &other = ch[c ^ 1];
-        const bool coop = C.upper <= coop_threshold && other.upper <= 2048;  // (a nearly finished chain leaves the GPU idle too)
-        const int batch = coop ? 16 : 8;
+        static const int policy = getenv("RT_COOP_POLICY") ? atoi(getenv("RT_COOP_POLICY")) : 1;
+        const bool coop = C.upper <= coop_threshold && (policy == 0 || other.upper <= 2048);
+        // a launch of the priority chain has to wait for blocks of the other chain to retire before it gets SM
+        // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
+        static const int coop_mult = getenv("RT_COOP_MULT") ? atoi(getenv("RT_COOP_MULT")) : 4;
+        const int batch = coop ? 4 : 8;
+        const int att = coop ? attempts * coop_mult : attempts;
         for (int b = 0; b < batch; b++, C.k++) {
           const int k = C.k;
           if (coop)
-            rt_integrate_kernel<MODE, true><<<grid_for(C.upper * 8, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
+            rt_integrate_kernel<MODE, true><<<grid_for(C.upper, (RT_BLOCK / 32) * RT_COOP_RAYS_PER_WARP), RT_BLOCK, smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
-                C.cnt + ((k + 2) % 3), attempts);
+                C.cnt + ((k + 2) % 3), att);
           else
             rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
-                C.cnt + ((k + 2) % 3), attempts);
+                C.cnt + ((k + 2) % 3), att);
           C.cur ^= 1;
           ctx->stats.kernel_launches++;
           ctx->stats.slices++;

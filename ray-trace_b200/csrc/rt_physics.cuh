@@ -166,14 +166,20 @@ struct RtExtras2D {  // save_func by-products, RayTrace_lat.jl:318-324
 // is instantiated once (the kernel has to fit the instruction cache; with the evaluations inlined side by side
 // the first profile showed "no instruction" as the top stall).  point 0 = centre (with dmu/dpsi), 1/2 =
 // theta -/+ 5e-12, 3/4 = centre medium at f -/+ 5e-6.
-// Cooperative mode (COOP = true): a ray is owned by a group of 8 adjacent lanes that all hold the same state; the
-// five evaluations of the loop above are done by lanes 0..4 of the group IN PARALLEL (lanes 5..7 repeat the
-// centre) and exchanged with shuffles.  Every evaluation executes exactly the same instructions on the same
-// inputs as in the rolled loop, so the results are bit-identical; what changes is the latency of one RHS
-// (1 geometry + 1 Stix instead of 3 + 5), which is what bounds the straggler tail of a sweep.
-__device__ __forceinline__ unsigned rt_group_mask() { return 0xffu << (threadIdx.x & 24); }
+// Cooperative mode (rt_physics_fast.cuh, COOP = true): a ray is owned by a group of 3 adjacent lanes that all hold
+// the same state (10 rays per warp, lanes 30 and 31 idle).  The three theta points of the loop above are evaluated
+// by the three lanes IN PARALLEL, then lanes 0 and 1 take the two frequency points, and the results are exchanged
+// with shuffles.  Every evaluation executes the same instructions on the same inputs as in the one-thread-per-ray
+// code, so the results are bit-identical; what changes is the latency of one right-hand side (geometry + 2 Stix
+// evaluations instead of 3 + 5) at ~1.4x the issue cost, which is what the long dependent chains of the
+// magnetospherically reflected rays need.
+#define RT_COOP_LANES 3
+#define RT_COOP_RAYS_PER_WARP 10
+__device__ __forceinline__ int rt_group_rank() { const int l = threadIdx.x & 31; return l - 3 * ((l * 11) >> 5); }
+__device__ __forceinline__ int rt_group_base() { const int l = threadIdx.x & 31; return 3 * ((l * 11) >> 5); }
+__device__ __forceinline__ unsigned rt_group_mask() { return 7u << rt_group_base(); }
 __device__ __forceinline__ double rt_group_get(double x, int src) {
-  return __shfl_sync(rt_group_mask(), x, (threadIdx.x & 24) + src);
+  return __shfl_sync(rt_group_mask(), x, rt_group_base() + src);
 }
 
 struct RtFivePoint {
@@ -181,28 +187,13 @@ struct RtFivePoint {
 };
 
 // haselgrove!(du,u,p,t) 2D: RayTrace_lat.jl:251-273 (signs: RayMain.jl:341-342)
-template <int PRESET, bool COOP = false>
+template <int PRESET>
 __device__ __forceinline__ void rt_haselgrove_2d(const RtDevEnv &E, const double *u, double *du, RtExtras2D *ex) {
   const double r = u[0], th = u[1], chi = u[2], freq = u[3];
   const double two_pi = 2.0 * RT_PI;
   RtPlasma pc, p;
   double dip = 0.0, psi = 0.0;
   RtFivePoint m = {0, 0, 0, 0, 0, 0};
-  if (COOP) {
-    const int g = threadIdx.x & 7, k = (g < 5) ? g : 0;
-    double th_k = (k == 1) ? th - 1.0e-11 / 2.0 : ((k == 2) ? th + 1.0e-11 / 2.0 : th);
-    double f_k = (k == 3) ? freq - 1.0e-5 / 2.0 : ((k == 4) ? freq + 1.0e-5 / 2.0 : freq);
-    rt_geo2d<PRESET>(E, r, th_k, chi, p, dip, psi);  // lanes 0,3,4 (and 5..7) hold the centre dip/psi
-    RtMu v = rt_stix(p, two_pi * f_k, k == 0);
-    m.mu_c = rt_group_get(v.mu, 0);
-    m.dmudpsi = rt_group_get(v.dmudpsi, 0);
-    m.mu_tl = rt_group_get(v.mu, 1);
-    m.mu_tr = rt_group_get(v.mu, 2);
-    m.mu_fl = rt_group_get(v.mu, 3);
-    m.mu_fr = rt_group_get(v.mu, 4);
-    dip = rt_group_get(dip, 0);
-    psi = rt_group_get(psi, 0);
-  } else
 #pragma unroll 1
   for (int k = 0; k < 5; k++) {
     double f_k = freq;
@@ -300,30 +291,11 @@ __device__ __forceinline__ double rt_ddrho(const RtGeo3D &g, const RtMu &c, doub
 }
 
 // haselgrove!(du,u,p,t) 3D: RayTrace_3D.jl:327-359; u = (r,theta,phi,rho_r,rho_theta,rho_phi,T), p = [freq]
-template <bool COOP = false>
 __device__ __forceinline__ void rt_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, double *du) {
   const double r = u[0], th = u[1], rr_ = u[3], rt_ = u[4], rp_ = u[5];
   const double two_pi = 2.0 * RT_PI;
   RtGeo3D gc, g;
   RtFivePoint m = {0, 0, 0, 0, 0, 0};
-  if (COOP) {
-    const int gl = threadIdx.x & 7, k = (gl < 5) ? gl : 0;
-    double th_k = (k == 1) ? th - 1.0e-11 / 2.0 : ((k == 2) ? th + 1.0e-11 / 2.0 : th);
-    double f_k = (k == 3) ? freq - 1.0e-5 / 2.0 : ((k == 4) ? freq + 1.0e-5 / 2.0 : freq);
-    rt_geo3d(E, r, th_k, rr_, rt_, rp_, g);
-    RtMu v = rt_stix(g.p, two_pi * f_k, k == 0);
-    m.mu_c = rt_group_get(v.mu, 0);
-    m.dmudpsi = rt_group_get(v.dmudpsi, 0);
-    m.mu_tl = rt_group_get(v.mu, 1);
-    m.mu_tr = rt_group_get(v.mu, 2);
-    m.mu_fl = rt_group_get(v.mu, 3);
-    m.mu_fr = rt_group_get(v.mu, 4);
-    gc.Br = rt_group_get(g.Br, 0);  // centre geometry for the Kimura terms (lanes 1, 2 hold theta -/+)
-    gc.Bt = rt_group_get(g.Bt, 0);
-    gc.Bp = rt_group_get(g.Bp, 0);
-    gc.p.s = rt_group_get(g.p.s, 0);
-    gc.p.c = rt_group_get(g.p.c, 0);
-  } else
 #pragma unroll 1
   for (int k = 0; k < 5; k++) {
     double f_k = freq;

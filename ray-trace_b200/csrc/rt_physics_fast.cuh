@@ -194,8 +194,9 @@ template <bool COOP>
 RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, double *du) {
   const double r = u[0], th = u[1], rr_ = u[3], rt_ = u[4], rp_ = u[5];
   bool ok = true;
-  // r >= 2^16 (so that r -+ 5e-12 == r and d(mu)/dr is (mu - mu)/1e-11) and below 2^513; rho_phi finite, non-zero
-  ok = ok && ((unsigned)(__double2hiint(r) - 0x40f00000) < (0x60000000u - 0x40f00000u));
+  // 2^16 <= |r| < 2^513 (so that r -+ 5e-12 == r and d(mu)/dr is (mu - mu)/1e-11; trial stages overshoot to
+  // negative radii routinely); rho_phi finite, non-zero
+  ok = ok && ((unsigned)((__double2hiint(r) & 0x7fffffff) - 0x40f00000) < (0x60000000u - 0x40f00000u));
   ok = ok && rtf_quarter_range(rp_);
   const double two_pi = 2.0 * RT_PI;
   RtRad3D Rd;
@@ -204,23 +205,30 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
   RtMu c;
   double mu_tl, mu_tr, mu_fl, mu_fr;
   if (COOP) {
-    const int gl = threadIdx.x & 7, k = (gl < 5) ? gl : 0;
+    // lane rank 0 / 1 / 2 of the ray's group: theta, theta - 5e-12, theta + 5e-12 (geometry + Stix side by side),
+    // then ranks 0 / 1: centre medium at f - 5e-6 / f + 5e-6 (rank 2 repeats f + 5e-6, unused)
+    const int k = rt_group_rank();
     const double th_k = (k == 1) ? th - 1.0e-11 / 2.0 : ((k == 2) ? th + 1.0e-11 / 2.0 : th);
-    const double f_k = (k == 3) ? freq - 1.0e-5 / 2.0 : ((k == 4) ? freq + 1.0e-5 / 2.0 : freq);
     RtGeo3D g;
     rtf_geo3d(E, Rd, r, th_k, rr_, rt_, g, ok);
-    RtMu v = rtf_stix<true>(g.p, two_pi * f_k, ok);
+    RtMu v = rtf_stix<true>(g.p, two_pi * freq, ok);
+    gc.Br = rt_group_get(g.Br, 0);
+    gc.Bt = rt_group_get(g.Bt, 0);
+    gc.Bmag = rt_group_get(g.Bmag, 0);
+    gc.p.w_e2 = rt_group_get(g.p.w_e2, 0);
+    gc.p.w_p2 = rt_group_get(g.p.w_p2, 0);
+    gc.p.W_e = rt_group_get(g.p.W_e, 0);
+    gc.p.W_p = rt_group_get(g.p.W_p, 0);
+    gc.p.s = rt_group_get(g.p.s, 0);
+    gc.p.c = rt_group_get(g.p.c, 0);
+    const double f_k = (k == 0) ? freq - 1.0e-5 / 2.0 : freq + 1.0e-5 / 2.0;
+    const double m2 = rtf_stix<false>(gc.p, two_pi * f_k, ok).mu;
     c.mu = rt_group_get(v.mu, 0);
     c.dmudpsi = rt_group_get(v.dmudpsi, 0);
     mu_tl = rt_group_get(v.mu, 1);
     mu_tr = rt_group_get(v.mu, 2);
-    mu_fl = rt_group_get(v.mu, 3);
-    mu_fr = rt_group_get(v.mu, 4);
-    gc.Br = rt_group_get(g.Br, 0);
-    gc.Bt = rt_group_get(g.Bt, 0);
-    gc.Bmag = rt_group_get(g.Bmag, 0);
-    gc.p.s = rt_group_get(g.p.s, 0);
-    gc.p.c = rt_group_get(g.p.c, 0);
+    mu_fl = rt_group_get(m2, 0);
+    mu_fr = rt_group_get(m2, 1);
   } else {
     // centre first (with d(mu)/d(psi)); the theta -/+ and f -/+ pairs are loops so that the build can choose
     // between rolled (small register footprint, more resident warps) and unrolled (more chains per warp)
@@ -294,25 +302,32 @@ template <bool COOP>
 RTF bool rtf_haselgrove_2d_lat(const RtDevEnv &E, const double *u, double *du, RtExtras2D *ex) {
   const double r = u[0], th = u[1], chi = u[2], freq = u[3];
   bool ok = true;
-  ok = ok && ((unsigned)(__double2hiint(r) - 0x40f00000) < (0x60000000u - 0x40f00000u));
+  ok = ok && ((unsigned)((__double2hiint(r) & 0x7fffffff) - 0x40f00000) < (0x60000000u - 0x40f00000u));
   const double two_pi = 2.0 * RT_PI;
   RtRad2D Rd;
   rtf_rad2d(E, r, Rd, ok);
   RtMu c;
   double mu_tl, mu_tr, mu_fl, mu_fr, dip, psi;
   if (COOP) {
-    const int gl = threadIdx.x & 7, k = (gl < 5) ? gl : 0;
+    const int k = rt_group_rank();
     const double th_k = (k == 1) ? th - 1.0e-11 / 2.0 : ((k == 2) ? th + 1.0e-11 / 2.0 : th);
-    const double f_k = (k == 3) ? freq - 1.0e-5 / 2.0 : ((k == 4) ? freq + 1.0e-5 / 2.0 : freq);
-    RtPlasma p;
+    RtPlasma p, pc;
     rtf_geo2d_lat(E, Rd, r, th_k, chi, p, dip, psi, ok);
-    RtMu v = rtf_stix<true>(p, two_pi * f_k, ok);
+    RtMu v = rtf_stix<true>(p, two_pi * freq, ok);
+    pc.w_e2 = rt_group_get(p.w_e2, 0);
+    pc.w_p2 = rt_group_get(p.w_p2, 0);
+    pc.W_e = rt_group_get(p.W_e, 0);
+    pc.W_p = rt_group_get(p.W_p, 0);
+    pc.s = rt_group_get(p.s, 0);
+    pc.c = rt_group_get(p.c, 0);
+    const double f_k = (k == 0) ? freq - 1.0e-5 / 2.0 : freq + 1.0e-5 / 2.0;
+    const double m2 = rtf_stix<false>(pc, two_pi * f_k, ok).mu;
     c.mu = rt_group_get(v.mu, 0);
     c.dmudpsi = rt_group_get(v.dmudpsi, 0);
     mu_tl = rt_group_get(v.mu, 1);
     mu_tr = rt_group_get(v.mu, 2);
-    mu_fl = rt_group_get(v.mu, 3);
-    mu_fr = rt_group_get(v.mu, 4);
+    mu_fl = rt_group_get(m2, 0);
+    mu_fr = rt_group_get(m2, 1);
     dip = rt_group_get(dip, 0);
     psi = rt_group_get(psi, 0);
   } else {
