@@ -81,7 +81,7 @@ typedef struct rt_solver_opts {
   double reltol, abstol; /* 1e-7 / 1e-6 (2D call), 1e-3 / 1e-6 (3D defaults) */
   double dtmax, dtmin;   /* 1e6 / 1e-8 (2D call); <= 0 means t1 - t0 / 0 */
   double r_esc;          /* [EXT] escape radius in metres, <= 0 disables */
-  int32_t slice_attempts;/* step attempts per kernel launch between compactions (0 = default 8) */
+  int32_t slice_attempts;/* step attempts per kernel launch between compactions (0 = default 4) */
   int32_t coop_threshold;/* live-ray count at or below which 3 lanes share one ray (0 = default 10000, < 0 = never) */
   int32_t single_chain;  /* 0 = rays that start upward run as a separate, prioritised chain of launches; 1 = one chain */
   int32_t reserved;

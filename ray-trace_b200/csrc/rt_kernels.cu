@@ -560,7 +560,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
-  const int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 8;
+  const int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 4;
   const bool two_chains = ctx->opts.single_chain == 0;
   ctx->stats = rt_stats{};
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
@@ -609,7 +609,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
             cudaEventRecord(ctx->ev[2], C.st);
             cudaEventSynchronize(ctx->ev[2]);
             cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]);
-            fprintf(stderr, "[rt] chain %d after %d slices (%d attempts): active=%lld t=%.2f ms\n", c, C.k, C.k * attempts /* nominal */,
+            fprintf(stderr, "[rt] chain %d after %d slices (%d attempts): active=%lld t=%.2f ms\n", c, C.k, C.k * attempts /* nominal: cooperative slices are longer */,
                     C.upper, ms);
           }
         } else if (q != cudaErrorNotReady) {
@@ -625,9 +625,9 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         const bool coop = C.upper <= coop_threshold && (policy == 0 || other.upper <= 2048);
         // a launch of the priority chain has to wait for blocks of the other chain to retire before it gets SM
         // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
-        static const int coop_mult = getenv("RT_COOP_MULT") ? atoi(getenv("RT_COOP_MULT")) : 4;
+        static const int coop_att = getenv("RT_COOP_ATT") ? atoi(getenv("RT_COOP_ATT")) : 32;
         const int batch = coop ? 4 : 8;
-        const int att = coop ? attempts * coop_mult : attempts;
+        const int att = coop ? (attempts > coop_att ? attempts : coop_att) : attempts;
         for (int b = 0; b < batch; b++, C.k++) {
           const int k = C.k;
           if (coop)
