@@ -20,6 +20,9 @@
 #include "rt_physics_fast.cuh"
 
 #define RT_BLOCK 128
+#ifndef RT_COOP_MINBLOCKS
+#define RT_COOP_MINBLOCKS 1
+#endif
 #ifndef RT_MINBLOCKS
 #define RT_MINBLOCKS 3  // __launch_bounds__ second argument for the integrate kernels (register budget)
 #endif
@@ -185,6 +188,22 @@ __device__ __forceinline__ double rt_rms(const double *v, const double *sk) {
   return RT_SQRT(s / (double)DIM);
 }
 
+// EEst = sqrt(mean((e_i / sk_i)^2)) with IEEE division and sqrt (cold path of the kernel's error norm)
+template <int DIM>
+struct RtErrIn {
+  double e[DIM], sk[DIM];
+};
+template <int DIM>
+__device__ __noinline__ double rt_eest_exact(RtErrIn<DIM> in) {
+  double s = 0.0;
+#pragma unroll
+  for (int c = 0; c < DIM; c++) {
+    double q = in.e[c] / in.sk[c];
+    s = s + q * q;
+  }
+  return RT_SQRT(s / (double)DIM);
+}
+
 // Append ray i to the next launch's work list (warp-aggregated atomic).
 __device__ __forceinline__ void rt_enqueue(bool pred, int i, int *idx_out, int *count_out) {
   unsigned m = __ballot_sync(0xffffffffu, pred);
@@ -299,7 +318,7 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(const __grid_constant
 
 // ---- the slice kernel -----------------------------------------------------------------------------
 template <int MODE, bool COOP>
-__global__ void __launch_bounds__(RT_BLOCK, COOP ? 1 : RT_MINBLOCKS)  // COOP runs a few warps per SM: no register cap
+__global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLOCKS)  // COOP runs a few warps per SM: no register cap
     rt_integrate_kernel(const __grid_constant__ RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in,
                         const int *__restrict__ count_in, int *idx_out, int *count_out, int *count_clear,
                         int attempts) {
@@ -361,12 +380,25 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? 1 : RT_MINBLOCKS)  // COOP ru
 
     // stages 2..7: y = u + h * sum_j a_sj k_j (left to right), k_s = f(y)
     for (int s = 0; s < 6; s++) {
-#pragma unroll
-      for (int c = 0; c < DIM; c++) {
-        double acc = RT_A[s][0] * RT_K(0, c);
-        for (int q = 1; q <= s; q++) acc = acc + RT_A[s][q] * RT_K(q, c);
-        y[c] = u[c] + h * acc;
+      // one specialised, fully unrolled sum per stage row (all shared-memory loads up front, DIM independent
+      // chains) instead of a rolled loop over the row: same left-to-right order, hence the same bits
+#define RT_STAGE_ROW(S)                                                      \
+  case S: {                                                                  \
+    _Pragma("unroll") for (int c = 0; c < DIM; c++) {                        \
+      double acc = RT_A[S][0] * RT_K(0, c);                                  \
+      _Pragma("unroll") for (int q = 1; q <= S; q++) acc = acc + RT_A[S][q] * RT_K(q, c); \
+      y[c] = u[c] + h * acc;                                                 \
+    }                                                                        \
+  } break;
+      switch (s) {
+        RT_STAGE_ROW(0)
+        RT_STAGE_ROW(1)
+        RT_STAGE_ROW(2)
+        RT_STAGE_ROW(3)
+        RT_STAGE_ROW(4)
+        RT_STAGE_ROW(5)
       }
+#undef RT_STAGE_ROW
       double dy[DIM];
       rt_rhs<MODE, COOP>(E, y, par, dy, &ex);
 #pragma unroll
@@ -378,7 +410,10 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? 1 : RT_MINBLOCKS)  // COOP ru
 
     double hnew = h;
     if (O.adaptive) {
+      // error norm: branch-free divisions / sqrt first; the exact ones, out of line, when their flag says no
+      double ev[DIM], skv[DIM];
       double ssum = 0.0;
+      bool okE = true;
 #pragma unroll
       for (int c = 0; c < DIM; c++) {
         double acc = RT_BT[0] * RT_K(0, c);
@@ -387,10 +422,25 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? 1 : RT_MINBLOCKS)  // COOP ru
         double e = h * acc;
         double a0 = rt_abs(u[c]), a1 = rt_abs(un[c]);
         double sk = O.abstol + ((a0 > a1) ? a0 : a1) * O.reltol;
-        double qq = e / sk;
+        ev[c] = e;
+        skv[c] = sk;
+        bool okq = true;
+        double qq = rtf_div(e, sk, okq);
+        const bool z = (e == 0.0) && (sk > 0.0);  // +-0 / positive = +-0
+        qq = z ? e : qq;
+        okE = okE && (okq || z);
         ssum = ssum + qq * qq;
       }
-      double EEst = RT_SQRT(ssum / (double)DIM);
+      double EEst = rtf_sqrt(rtf_div(ssum, (double)DIM, okE), okE);
+      if (!okE) {
+        RtErrIn<DIM> in;
+#pragma unroll
+        for (int c = 0; c < DIM; c++) {
+          in.e[c] = ev[c];
+          in.sk[c] = skv[c];
+        }
+        EEst = rt_eest_exact<DIM>(in);
+      }
       if (!(EEst <= 1.0)) {  // reject (NaN included)
         nreject++;
         if (EEst != EEst) {
