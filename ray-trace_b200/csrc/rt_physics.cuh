@@ -181,6 +181,13 @@ __device__ __forceinline__ unsigned rt_group_mask() { return 7u << rt_group_base
 __device__ __forceinline__ double rt_group_get(double x, int src) {
   return __shfl_sync(rt_group_mask(), x, rt_group_base() + src);
 }
+// true when `pred` holds on all three lanes of the group.  Three shuffles: a __ballot_sync with a per-group mask
+// compiles to a loop over the warp's distinct masks (10 VOTE iterations per call in the first cooperative profile).
+__device__ __forceinline__ bool rt_group_all(bool pred) {
+  const unsigned m = rt_group_mask();
+  const int b = rt_group_base(), v = pred ? 1 : 0;
+  return (__shfl_sync(m, v, b) & __shfl_sync(m, v, b + 1) & __shfl_sync(m, v, b + 2)) != 0;
+}
 
 struct RtFivePoint {
   double mu_c, dmudpsi, mu_tl, mu_tr, mu_fl, mu_fr;

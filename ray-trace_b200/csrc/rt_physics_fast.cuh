@@ -254,7 +254,7 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
   }
   ok = ok && rtf_quarter_range(gc.Bmag);
   rtf_tail3d(E, Rd, u, freq, gc, c.mu, c.dmudpsi, mu_tl, mu_tr, mu_fl, mu_fr, du, ok);
-  if (COOP) ok = (__ballot_sync(rt_group_mask(), ok) | ~rt_group_mask()) == 0xffffffffu;
+  if (COOP) ok = rt_group_all(ok);
   return ok;
 }
 
@@ -371,6 +371,6 @@ RTF bool rtf_haselgrove_2d_lat(const RtDevEnv &E, const double *u, double *du, R
     ex->dip = dip;
     ex->psi = psi;
   }
-  if (COOP) ok = (__ballot_sync(rt_group_mask(), ok) | ~rt_group_mask()) == 0xffffffffu;
+  if (COOP) ok = rt_group_all(ok);
   return ok;
 }
