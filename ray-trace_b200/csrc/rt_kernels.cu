@@ -618,11 +618,12 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
       }
       if (!C.pending && C.upper > 0) {
         // 3 lanes per ray (rt_physics.cuh) buys latency (0.45x per right-hand side) with throughput (1.4x the issue
-        // slots): used once a chain is down to its long rays.  RT_COOP_POLICY=0 (developer switch) lifts the restriction to
-        // the time when the other chain is all but finished.
+        // slots): used once a chain is down to its long rays AND the two chains together no longer fill the GPU
+        // (measured: 25 us per attempt with 7 k rays on the GPU, 35 us with 14 k, 60 us with 27 k;
+        // tools/gpu_coop_density.py).  RT_COOP_POLICY=0 (developer switch) drops the second condition.
         const Chain &other = ch[c ^ 1];
         static const int policy = getenv("RT_COOP_POLICY") ? atoi(getenv("RT_COOP_POLICY")) : 1;
-        const bool coop = C.upper <= coop_threshold && (policy == 0 || other.upper <= 2048);
+        const bool coop = C.upper <= coop_threshold && (policy == 0 || C.upper + other.upper <= coop_threshold + 2048);
         // a launch of the priority chain has to wait for blocks of the other chain to retire before it gets SM
         // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
         static const int coop_att = getenv("RT_COOP_ATT") ? atoi(getenv("RT_COOP_ATT")) : 32;
