@@ -33,6 +33,10 @@ RE = 6.3712e6
 # DADD + DMUL + 2*DFMA per RHS of the minimal faithful schedule, calibrated once with ncu
 # (profiles/r1_flop_calibration.md) and frozen.
 FLOP_PER_RHS = {"cfg3": 2602.0, "cfg2": 2307.0}
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE full-list launch of rt_integrate_kernel (4 attempts for each of
+# 956 000 rays) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v2.md: 175.3 MB + 115.0 MB.
+# Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 956 000 = 0.38 GB-equivalent upper bound.
+NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 290.3e6, "cfg2": None}
 
 
 def parse():
@@ -260,6 +264,18 @@ def main():
     ms_local = sum(a.elapsed_time(b) for a, b in ev)
     nfe_local = int(ints[3].to(torch.int64).sum().item())
     status_h = ints[0].cpu().numpy()
+    # diagnostic, outside the timed region: the integrate kernel in steady state (every ray alive, full lists):
+    # the same sweep cut off after 24 step attempts, one chain
+    steady = None
+    if rank == 0:
+        kw = solver_kwargs(args.workload, args.slice)
+        rt.set_solver(**dict(kw, maxiters=24, single_chain=1))
+        rt.solve_device(n, cols, res_ptrs)
+        st2 = rt.solve_device(n, cols, res_ptrs)
+        nfe2 = int(ints[3].to(torch.int64).sum().item())
+        steady = {"rhs_evals_per_s": nfe2 / (st2.integrate_ms * 1e-3), "launches": int(st2.slices),
+                  "how": "same launch list, maxiters=24, single chain: integrate launches over full work lists only"}
+        rt.set_solver(**dict(kw, single_chain=0))
 
     # e2e: pinned host buffers through the host-pointer entry point (H2D + D2H inside the timed region)
     launch_p = torch.from_numpy(launch_h).pin_memory()
@@ -331,7 +347,12 @@ def main():
                        "partition": f"contiguous x{world}", "l2": "flushed between timed steps (256 MiB fill)",
                        "status_counts_rank0": {R.STATUS_NAMES[int(a)]: int(b) for a, b in zip(uniq, cnt)}},
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak / 1e12, "unit": "TFLOP/s",
-                         "frac": achieved / (peak / 1e12), "traffic": None,
+                         "frac": achieved / (peak / 1e12), "traffic": NCU_DRAM_BYTES_PER_FULL_LAUNCH[args.workload],
+                         "traffic_note": "bytes per full-list launch (ncu, profiles/r1_ncu_integrate_v2.md); "
+                                         "0.09 TB/s: HBM is not the bound",
+                         "steady_state": None if steady is None else dict(
+                             steady, achieved=steady["rhs_evals_per_s"] * flop / 1e12,
+                             frac=steady["rhs_evals_per_s"] * flop / peak),
                          "peak_source": "DFMA-chain microbenchmark in this run (MEASURED_PEAKS.json has no FP64 entry)",
                          "flop_per_rhs": flop, "kernel": "rt_integrate_kernel",
                          "avg_launch_ms": integ_ms / max(slices, 1), "launches": int(slices)},

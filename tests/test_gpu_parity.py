@@ -114,7 +114,7 @@ def test_solve_2d_fixed_step_bitexact(coop):
     rt.close()
 
 
-# coop_threshold: -1 = one thread per ray throughout; 0 = default (these small batches then run entirely with 8 lanes
+# coop_threshold: -1 = one thread per ray throughout; 0 = default (these small batches then run entirely with 3 lanes
 # per ray); 150 = switch from one mode to the other in the middle of the solve
 @pytest.mark.parametrize("coop", [-1, 0, 150])
 @pytest.mark.parametrize("name,pid", PRESETS_2D)
@@ -169,4 +169,90 @@ def test_trajectories_match_oracle_3d_with_stride(coop):
     for k in range(launch.shape[1]):
         ref = O.solve_ray_3d(E, o, launch[:7, k], launch[7, k], launch[8, k], cap=64)
         assert _same(res.trajectory(k), ref.traj)
+    rt.close()
+
+
+# ---- the branch-free primitives, the scheduler, and full-size properties -----------------------------------------
+def test_branch_free_primitives_bit_equal_exact_ones():
+    """rt_fast.cuh against IEEE division / sqrt and rt_math.h on pseudo-random operands, on the device."""
+    import ctypes as C
+    cnt = (C.c_ulonglong * 30)()
+    assert R.api._lib().rt_selftest_fastmath(0, C.c_longlong(200), C.c_ulonglong(2024), cnt, 30) == 0
+    for k in range(10):
+        compared, mism, flagged = cnt[3 * k], cnt[3 * k + 1], cnt[3 * k + 2]
+        assert compared > 5_000_000 and mism == 0, (k, compared, mism, flagged)
+
+
+def test_two_chains_and_one_chain_give_identical_results():
+    """Rays that start upward go to the priority chain (scheduling only)."""
+    launch = sweeps.sweep_3d(12, 3, 24)
+    out = []
+    for single in (0, 1):
+        rt = R.RayTracer("ray3d")
+        rt.set_solver(maxiters=600, r_esc=10 * RE, single_chain=single, coop_threshold=64)
+        res = rt.solve(launch)
+        assert (res.stats.prio_rays > 0) == (single == 0)
+        out.append(res)
+        rt.close()
+    a, b = out
+    for k in ("u_end", "t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
+        assert _same(getattr(a, k), getattr(b, k)), k
+    ref = O.solve_batch(O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, maxiters=600, r_esc=10 * RE), launch, True, 8)
+    _check_solve(a, ref, 1e-7)
+    assert 4 in set(np.unique(a.status))  # the long rays hit the iteration cap here
+
+
+def test_cfg3_full_size_properties_and_partition():
+    """BASELINE.json configs[2] at full size (10^6 rays): size-independent properties.  Every ray ends on the Earth's
+    surface (event root to rounding); counters are consistent; the result does not depend on how the launch list is
+    scheduled (one chain / two chains) or partitioned (multi-GPU sharding is a launch-list partition); mu does not
+    depend on longitude (RayTrace_3D.jl:54-66), so the 100 longitudes of one (colatitude, chi) cell agree up to the
+    step-size controller's phi-dependent error weight."""
+    import ctypes as C
+    full = sweeps.sweep_3d()
+    n = full.shape[1]
+    rt = R.RayTracer("ray3d")
+    rt.set_solver(r_esc=10 * RE)
+    res = rt.solve(full)
+    fb = (C.c_ulonglong * 8)()
+    R.api._lib().rt_debug_fallback_counts(rt._ctx, fb, 1)
+    assert set(np.unique(res.status)) == {2}  # every ray of this sweep ends on the Earth
+    assert int(res.nfe.astype(np.int64).sum()) == 285546464  # the workload bench.py quotes
+    assert np.array_equal(res.nfe, 6 * (res.naccept + res.nreject) + 2)
+    assert np.max(np.abs(res.u_end[0] - RE)) < 1e-6 and np.all(res.t_end > 0)  # metres: bisection to 1 ulp in theta
+    assert _same(res.group_delay, res.u_end[6])
+    assert fb[0] < 1e-3 * res.nfe.astype(np.int64).sum()  # the exact path is the rare path
+    cube = lambda a: a.reshape(100, 100, 100)  # (colat, lon, chi)
+    short = cube(res.naccept + res.nreject).max(axis=1) < 64  # cells of rays that go straight down
+    t = cube(res.t_end)
+    spread = (t.max(axis=1) - t.min(axis=1)) / t.mean(axis=1)
+    assert short.mean() > 0.9 and np.max(spread[short]) < 5e-2  # solver tolerance is 1e-3
+    # scheduling invariance: one chain, different slice length
+    rt.set_solver(r_esc=10 * RE, single_chain=1, slice_attempts=7)
+    one = rt.solve(full)
+    for k in ("u_end", "t_end", "status", "naccept", "nreject", "nreflect"):
+        assert _same(getattr(one, k), getattr(res, k)), k
+    # partition invariance: the 3rd of 8 contiguous parts
+    rt.set_solver(r_esc=10 * RE, single_chain=0, slice_attempts=0)
+    lo, hi = sweeps.partition(n, 2, 8)
+    part = rt.solve(np.ascontiguousarray(full[:, lo:hi]))
+    for k in ("t_end", "status", "naccept", "nfe"):
+        assert _same(getattr(part, k), getattr(res, k)[lo:hi]), k
+    assert _same(part.u_end, res.u_end[:, lo:hi])
+    rt.close()
+
+
+def test_cfg2_size_2d_sweep_capped_matches_oracle_sample():
+    """BASELINE.json configs[1] launch grid at full size (10^5 rays), iteration cap lowered so that the sweep takes
+    seconds; a strided sample of it against the oracle, and statuses/counters consistent everywhere."""
+    full = sweeps.sweep_2d()
+    rt = R.RayTracer("lat2d")
+    rt.set_solver(maxiters=400, r_esc=10 * RE)
+    res = rt.solve(full)
+    assert np.array_equal(res.nfe, 6 * (res.naccept + res.nreject) + 2)
+    assert np.all((res.status == 4) == (res.naccept + res.nreject >= 400))
+    idx = np.arange(0, full.shape[1], 997)
+    ref = O.solve_batch(O.env(O.LAT2D), O.opts(maxiters=400, r_esc=10 * RE), np.ascontiguousarray(full[:, idx]), False, 8)
+    assert _same(res.u_end[:, idx], ref["u_end"]) and _same(res.t_end[idx], ref["t_end"])
+    assert np.array_equal(res.status[idx], ref["status"]) and np.array_equal(res.nfe[idx], ref["nfe"])
     rt.close()
