@@ -3,7 +3,7 @@
 
 Workload (config.workload): "cfg3" = BASELINE.json configs[2], the 3D (RayTrace_3D.jl) sweep of 10^6 rays over
 colatitude x longitude x wave-normal angle that north_star's target is quoted on.  At N GPUs the sweep is refined
-along longitude to N*10^6 rays and partitioned contiguously (weak scaling, no data-path collective); the one
+along longitude to N*10^6 rays and partitioned across ranks (strided: rank, rank + N, ...) (weak scaling, no data-path collective); the one
 exchange is the gather of terminal records to rank 0 (inside the timed step for N > 1).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3|cfg2] [--impl ours|reference]
@@ -36,6 +36,8 @@ FLOP_PER_RHS = {"cfg3": 2602.0, "cfg2": 2307.0}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-list launch of rt_integrate_kernel (4 attempts for each of
 # 956 000 rays) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v2.md: 175.3 MB + 115.0 MB.
 # Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 956 000 = 0.38 GB-equivalent upper bound.
+# launch-list partition across ranks: strided (rank, rank + N, ...) so that every GPU gets its share of the long rays
+PARTITION = "strided"
 NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 290.3e6, "cfg2": None}
 
 
@@ -53,7 +55,7 @@ def parse():
 
 
 def make_launch(workload, world, rank, rays_per_gpu=0):
-    """This rank's contiguous partition of the (weak-scaled) sweep; returns (launch [ncol, n_local], n_total)."""
+    """This rank's partition of the (weak-scaled) sweep; returns (launch [ncol, n_local], n_total)."""
     from raytrace_b200 import sweeps
     if workload == "cfg3":
         if rays_per_gpu:
@@ -67,8 +69,7 @@ def make_launch(workload, world, rank, rays_per_gpu=0):
         else:
             full = sweeps.sweep_2d(400 * world, 250)
     n_total = full.shape[1]
-    lo, hi = sweeps.partition(n_total, rank, world)
-    return np.ascontiguousarray(full[:, lo:hi]), n_total
+    return np.ascontiguousarray(full[:, sweeps.partition_indices(n_total, rank, world, PARTITION)]), n_total
 
 
 def solver_kwargs(workload, slice_attempts=0):
@@ -239,7 +240,7 @@ def main():
         st = rt.solve_device(n, cols, res_ptrs)
         if world > 1:
             d, i = multi.pack_terminal(u_end, t_end, gd, ints[0], ints[1], ints[2], ints[3], ints[4])
-            multi.gather_terminal(d, i, n_total, rank, world)
+            multi.gather_terminal(d, i, n_total, rank, world, layout=PARTITION)
         return st
 
     for _ in range(args.warmup):
@@ -344,7 +345,7 @@ def main():
             "rays_per_s": rays_all * K / (ms_all * 1e-3),
             "config": {"workload": args.workload, "rays_total": int(rays_all), "rays_per_gpu": int(n),
                        "rhs_evals_per_step": int(nfe_all), "solver": solver_kwargs(args.workload, args.slice),
-                       "partition": f"contiguous x{world}", "l2": "flushed between timed steps (256 MiB fill)",
+                       "partition": f"{PARTITION} x{world}", "l2": "flushed between timed steps (256 MiB fill)",
                        "status_counts_rank0": {R.STATUS_NAMES[int(a)]: int(b) for a, b in zip(uniq, cnt)}},
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak / 1e12, "unit": "TFLOP/s",
                          "frac": achieved / (peak / 1e12), "traffic": NCU_DRAM_BYTES_PER_FULL_LAUNCH[args.workload],

@@ -5,7 +5,7 @@ Works on any torch.distributed backend (nccl on the GPU box; gloo in the CPU tes
 import torch
 import torch.distributed as dist
 
-from .sweeps import partition  # noqa: F401  (re-exported)
+from .sweeps import partition, partition_indices  # noqa: F401  (re-exported)
 
 DOUBLE_ROWS_2D = 4 + 2  # u_end[4], t_end, group_delay
 DOUBLE_ROWS_3D = 7 + 2
@@ -19,12 +19,15 @@ def pack_terminal(u_end, t_end, group_delay, status, naccept, nreject, nfe, nref
     return d, i
 
 
-def gather_terminal(d, i, n_total, rank, world, dst=0, group=None):
-    """Gather per-rank records (contiguous partitions of n_total rays) to rank `dst`.
-    Returns (doubles [rows, n_total], ints [5, n_total]) on dst, (None, None) elsewhere."""
+def gather_terminal(d, i, n_total, rank, world, dst=0, group=None, layout="contiguous"):
+    """Gather per-rank records (partitions of n_total rays, see sweeps.partition_indices) to rank `dst`, in launch-list
+    order.  Returns (doubles [rows, n_total], ints [5, n_total]) on dst, (None, None) elsewhere."""
     if world == 1:
         return d, i
-    sizes = [partition(n_total, r, world)[1] - partition(n_total, r, world)[0] for r in range(world)]
+    if layout == "strided":
+        sizes = [len(range(r, n_total, world)) for r in range(world)]
+    else:
+        sizes = [partition(n_total, r, world)[1] - partition(n_total, r, world)[0] for r in range(world)]
     nmax = max(sizes)
 
     def padded(x):
@@ -44,6 +47,13 @@ def gather_terminal(d, i, n_total, rank, world, dst=0, group=None):
     dist.gather(ip, il, dst=dst, group=group)
     if rank != dst:
         return None, None
+    if layout == "strided":
+        D = dp.new_empty((dp.shape[0], n_total))
+        I = ip.new_empty((ip.shape[0], n_total))
+        for r in range(world):
+            D[:, r::world] = dl[r][:, : sizes[r]]
+            I[:, r::world] = il[r][:, : sizes[r]]
+        return D, I
     D = torch.cat([dl[r][:, : sizes[r]] for r in range(world)], dim=1)
     I = torch.cat([il[r][:, : sizes[r]] for r in range(world)], dim=1)
     return D, I

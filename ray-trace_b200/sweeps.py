@@ -44,3 +44,14 @@ def partition(n, rank, world):
     lo = (n * rank) // world
     hi = (n * (rank + 1)) // world
     return lo, hi
+
+
+def partition_indices(n, rank, world, layout="contiguous"):
+    """Launch-list indices of rank `rank`: "contiguous" = [lo, hi) as partition(); "strided" = rank, rank + world, ...
+    Rays are independent, so any partition gives the same per-ray results; strided balances sweeps whose expensive
+    rays cluster in one part of the launch list (cfg3: the long magnetospheric paths sit at high colatitude)."""
+    import numpy as _np
+    if layout == "strided":
+        return _np.arange(rank, n, world)
+    lo, hi = partition(n, rank, world)
+    return _np.arange(lo, hi)

@@ -23,7 +23,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, out_path, n_total):
+def _worker(rank, world, port, out_path, n_total, layout):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from raytrace_b200 import multi, sweeps
@@ -31,13 +31,12 @@ def _worker(rank, world, port, out_path, n_total):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     full = sweeps.sweep_3d(3, 7, 5)[:, :n_total]
-    lo, hi = multi.partition(n_total, rank, world)
-    part = np.ascontiguousarray(full[:, lo:hi])
+    part = np.ascontiguousarray(full[:, sweeps.partition_indices(n_total, rank, world, layout)])
     res = O.solve_batch(O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, r_esc=10 * sweeps.RE), part, True, 1)
     T = torch.from_numpy
     d, i = multi.pack_terminal(T(res["u_end"]), T(res["t_end"]), T(res["u_end"][6].copy()), T(res["status"]),
                                T(res["naccept"]), T(res["nreject"]), T(res["nfe"]), T(res["nreflect"]))
-    D, I = multi.gather_terminal(d, i, n_total, rank, world)
+    D, I = multi.gather_terminal(d, i, n_total, rank, world, layout=layout)
     if rank == 0:
         np.savez(out_path, D=D.numpy(), I=I.numpy())
     else:
@@ -46,11 +45,15 @@ def _worker(rank, world, port, out_path, n_total):
     dist.destroy_process_group()
 
 
-def test_two_rank_partition_and_gather(tmp_path):
+import pytest
+
+
+@pytest.mark.parametrize("layout", ["contiguous", "strided"])
+def test_two_rank_partition_and_gather(tmp_path, layout):
     from raytrace_b200 import sweeps
     n_total = 101  # odd: ragged partitions 50 + 51
     out = str(tmp_path / "gathered.npz")
-    tmp.spawn(_worker, args=(2, _free_port(), out, n_total), nprocs=2, join=True)
+    tmp.spawn(_worker, args=(2, _free_port(), out, n_total, layout), nprocs=2, join=True)
     got = np.load(out)
     full = sweeps.sweep_3d(3, 7, 5)[:, :n_total]
     ref = O.solve_batch(O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, r_esc=10 * sweeps.RE), full, True, 2)
