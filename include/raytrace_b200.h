@@ -135,6 +135,12 @@ RT_API int rt_haselgrove_2d(rt_ctx *ctx, int64_t n, const double *u, double *du)
 /* haselgrove!(du,u,p,t), RayTrace_3D.jl:327-359: u, du are [7][n], freq is p[1] per ray */
 RT_API int rt_haselgrove_3d(rt_ctx *ctx, int64_t n, const double *u, const double *freq, double *du);
 
+/* plasmasphere.jl as a batch evaluator: L_rlam :122, plasmasphere_eq :73-94, diffusive_equilibrium :96-106,
+ * ionosphere_eq :108-117 and ne_total = diffusive_equilibrium(r, plasmasphere_eq(L)) + ionosphere_eq(r) :171.
+ * out5 is [5][n]: L, plasmasphere_eq, diffusive_equilibrium, ionosphere_eq, ne_total (cm^-3).  Lppi, Lppo, ne_Lppi,
+ * the seasonal bracket and mlt come from the environment (2D presets only). */
+RT_API int rt_plasmasphere_density(rt_ctx *ctx, int64_t n, const double *r, const double *lam, double *out5);
+
 /* ---- the solve: ODEProblem + solve over a launch list --------------------------------------- */
 /* 2D launch list columns (r, theta, chi, f, t) as in README.md:11; RayTrace_lat.jl:333-338 */
 RT_API int rt_solve_2d(rt_ctx *ctx, int64_t n, const double *r, const double *theta,

@@ -232,6 +232,15 @@ class RayTracer:
             _check(_lib().rt_haselgrove_2d(self._ctx, C.c_int64(n), _ptr(u2), _ptr(du)), self._ctx)
         return du[:, 0] if single else du
 
+    def plasmasphere(self, r, lam):
+        """plasmasphere.jl, batched: returns dict(L=L_rλ(r,λ) :122, plasmasphere_eq :73, diffusive_equilibrium :96,
+        ionosphere_eq :108, ne_total :171), each [n], densities in cm^-3."""
+        n = max(np.size(r), np.size(lam))
+        r, lam = _f64(r, n), _f64(lam, n)
+        out = np.zeros((5, n))
+        _check(_lib().rt_plasmasphere_density(self._ctx, C.c_int64(n), _ptr(r), _ptr(lam), _ptr(out)), self._ctx)
+        return dict(zip(("L", "plasmasphere_eq", "diffusive_equilibrium", "ionosphere_eq", "ne_total"), out))
+
     # -- the solve ---------------------------------------------------------------------------------
     def solve(self, launch, with_trajectories=None):
         """Trace a launch list.  2D: columns (r, θ, χ, f, t) [5, n];  3D: (r, θ, ϕ, ρ_r, ρ_θ, ρ_ϕ, T0, f, t) [9, n]."""

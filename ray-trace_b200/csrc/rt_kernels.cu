@@ -460,6 +460,60 @@ extern "C" int rt_refractive_index_3d(rt_ctx *ctx, int64_t n, const double *r, c
   return RT_OK;
 }
 
+// plasmasphere.jl as a batch evaluator: L_rlam :122, plasmasphere_eq :73-94,
+// diffusive_equilibrium :96-106 (i = 1, T = 2500 K, alpha = 1), ionosphere_eq :108-117 and the composition
+// ne_total = diffusive_equilibrium(r, plasmasphere_eq(L)) + ionosphere_eq(r) :171.  The file's undefined globals are
+// taken from the environment: ne_Lppi (:88) = the :61 formula, `t` (:90) = mlt (both inside rt_env_params).
+// out = [L, plasmasphere_eq, diffusive_equilibrium, ionosphere_eq, ne_total][n], cm^-3.
+__global__ void rt_plasmasphere_kernel(const __grid_constant__ RtDevEnv E, long long n, const double *r, const double *lam,
+                                       double *out) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double ri = r[i];
+  const double c = rt_cos(lam[i]);
+  const double L = ri / (E.re * (c * c));
+  double ne_eq = 0.0;
+  if (L <= E.Lppi) {
+    ne_eq = rt_exp10((-0.3145 * L + 3.9043) + E.ca_coef * rt_exp((2.0 - L) / 1.5));
+  } else if (E.Lppi < L && L <= E.Lppo) {
+    ne_eq = E.ne_Lppi * rt_exp10((E.Lppi - L) / 0.1);
+  } else if (E.Lppo < L) {
+    ne_eq = E.ca_trough * rt_pow_m4p5(L) + (1.0 - rt_exp((2.0 - L) / 10.0));
+  }
+  const double T = 2500.0, rb = 7370000.0;
+  const double G = rb * (1.0 - rb / ri);
+  const double q = rb / 7370.0;
+  const double S = ((1.506 * T) * (q * q)) * (1.0 / 1.0);
+  const double ne_de = ne_eq * RT_SQRT(1.0 * rt_exp(-G / S));
+  const double ne_iono = 1e5 * rt_exp(-10.0 * ((ri / E.re) - 1.0471));
+  out[i] = L;
+  out[n + i] = ne_eq;
+  out[2 * n + i] = ne_de;
+  out[3 * n + i] = ne_iono;
+  out[4 * n + i] = ne_de + ne_iono;
+}
+
+extern "C" int rt_plasmasphere_density(rt_ctx *ctx, int64_t n, const double *r, const double *lam, double *out5) {
+  if (!ctx || n < 0 || (n > 0 && (!r || !lam || !out5)))
+    return set_err(ctx, RT_ERR_INVALID, "rt_plasmasphere_density: bad argument");
+  if (ctx->env.preset == RT_PRESET_RAY3D)
+    return set_err(ctx, RT_ERR_INVALID,
+                   "rt_plasmasphere_density: plasmasphere.jl uses the RayTrace_lat.jl seasonal term; the environment "
+                   "preset is RT_PRESET_RAY3D");
+  if (n == 0) return RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t nb = (size_t)n * sizeof(double);
+  if (int rc = ensure_stage(ctx, 7 * nb, 0)) return rc;
+  double *d = ctx->stage_d;
+  RT_CUDA(ctx, cudaMemcpyAsync(d, r, nb, cudaMemcpyHostToDevice, ctx->stream));
+  RT_CUDA(ctx, cudaMemcpyAsync(d + n, lam, nb, cudaMemcpyHostToDevice, ctx->stream));
+  rt_plasmasphere_kernel<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->denv, n, d, d + n, d + 2 * n);
+  RT_CUDA(ctx, cudaGetLastError());
+  RT_CUDA(ctx, cudaMemcpyAsync(out5, d + 2 * n, 5 * nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
 static int haselgrove_batch(rt_ctx *ctx, int64_t n, const double *u, const double *freq, double *du, bool want3d) {
   if (!ctx || n < 0 || (n > 0 && (!u || !du || (want3d && !freq))))
     return set_err(ctx, RT_ERR_INVALID, "rt_haselgrove: bad argument");
@@ -589,9 +643,17 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
     long long upper;
     int cur, k;
     bool pending;
-  } ch[2] = {{st, {ctx->idx[0], ctx->idx[1]}, ctx->count, ctx->h_count + 2, ctx->ev_chain[0], ctx->h_count[0], 0, 0, false},
+    int att;            // attempts per launch of the next batch (adaptive, see below)
+    long long nominal;  // attempts enqueued so far (diagnostics)
+  } ch[2] = {{st, {ctx->idx[0], ctx->idx[1]}, ctx->count, ctx->h_count + 2, ctx->ev_chain[0], ctx->h_count[0], 0, 0, false,
+              attempts, 0},
              {ctx->prio_stream, {ctx->idx_prio[0], ctx->idx_prio[1]}, ctx->count + 4, ctx->h_count + 3, ctx->ev_chain[1],
-              ctx->h_count[1], 0, 0, false}};
+              ctx->h_count[1], 0, 0, false, attempts, 0}};
+  // Slice length adapts when the caller did not fix it: a batch that lost fewer than 3 % of its rays doubles the
+  // next batch's attempts per launch (up to 64) — lists of long-lived rays (iteration-capped 2D sweeps, the
+  // magnetospheric paths) need no compaction, and fewer launches mean fewer waits for SM slots; any batch that
+  // does lose rays falls back to the base length.
+  const bool adapt = ctx->opts.slice_attempts <= 0;
   ctx->stats.prio_rays = ch[1].upper;
   if (ch[1].upper > 0) RT_CUDA(ctx, cudaStreamWaitEvent(ch[1].st, ctx->ev_fork, 0));
   const bool dbg = getenv("RT_DEBUG") != nullptr;
@@ -603,13 +665,15 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         cudaError_t q = cudaEventQuery(C.ev);
         if (q == cudaSuccess) {
           C.pending = false;
+          const long long before = C.upper;
           C.upper = *C.h;
+          if (adapt) C.att = (C.upper * 100 >= before * 97) ? (C.att * 2 > 64 ? 64 : C.att * 2) : attempts;
           if (dbg) {
             float ms = 0;
             cudaEventRecord(ctx->ev[2], C.st);
             cudaEventSynchronize(ctx->ev[2]);
             cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]);
-            fprintf(stderr, "[rt] chain %d after %d slices (%d attempts): active=%lld t=%.2f ms\n", c, C.k, C.k * attempts /* nominal: cooperative slices are longer */,
+            fprintf(stderr, "[rt] chain %d after %d slices (%lld attempts): active=%lld t=%.2f ms\n", c, C.k, C.nominal,
                     C.upper, ms);
           }
         } else if (q != cudaErrorNotReady) {
@@ -628,7 +692,8 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
         static const int coop_att = getenv("RT_COOP_ATT") ? atoi(getenv("RT_COOP_ATT")) : 32;
         const int batch = coop ? 4 : 8;
-        const int att = coop ? (attempts > coop_att ? attempts : coop_att) : attempts;
+        const int att = coop ? (C.att > coop_att ? C.att : coop_att) : C.att;
+        C.nominal += (long long)att * batch;
         for (int b = 0; b < batch; b++, C.k++) {
           const int k = C.k;
           if (coop)

@@ -55,3 +55,14 @@ def partition_indices(n, rank, world, layout="contiguous"):
         return _np.arange(rank, n, world)
     lo, hi = partition(n, rank, world)
     return _np.arange(lo, hi)
+
+
+def launch_angle(b, hbi=1.0e6, re=RE):
+    """Wave-normal launch angle helper of scratch.jl:725-731: for a ray leaving the ground at angle b from the
+    vertical, alpha = acos((re sin^2 b + cos b sqrt((re+hbi)^2 - re^2 sin^2 b)) / (re+hbi)) is the geocentric angle
+    travelled up to the launch altitude hbi and chi = b - alpha the wave-normal angle there.  Returns (alpha, chi)."""
+    import numpy as _np
+    b = _np.asarray(b, dtype=_np.float64)
+    alpha = _np.arccos((re * _np.sin(b) ** 2.0 + _np.cos(b) * ((re + hbi) ** 2.0 - re ** 2.0 * _np.sin(b) ** 2.0) ** 0.5)
+                       / (re + hbi))
+    return alpha, b - alpha

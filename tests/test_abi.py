@@ -100,3 +100,13 @@ def test_sweeps_are_the_named_configs():
     assert np.allclose(np.sum(b[3:6] ** 2, axis=0), 1.0)
     parts = [sweeps.partition(1000003, r, 8) for r in range(8)]
     assert parts[0][0] == 0 and parts[-1][1] == 1000003 and all(parts[i][1] == parts[i + 1][0] for i in range(7))
+
+
+def test_launch_angle_helper_reproduces_the_scratch_cell():
+    """scratch.jl:725-731 with hbi = 1e6, b = -pi/3."""
+    from raytrace_b200 import sweeps
+    import math
+    re, hbi, b = 6.3712e6, 1.0e6, -math.pi / 3
+    alpha = math.acos((re * math.sin(b) ** 2.0 + math.cos(b) * ((re + hbi) ** 2.0 - re ** 2.0 * math.sin(b) ** 2.0) ** 0.5) / (re + hbi))
+    a, chi = sweeps.launch_angle(b)
+    assert abs(a - alpha) < 1e-15 and abs(chi - (b - alpha)) < 1e-15 and 0 < a < 0.3

@@ -256,3 +256,27 @@ def test_cfg2_size_2d_sweep_capped_matches_oracle_sample():
     assert _same(res.u_end[:, idx], ref["u_end"]) and _same(res.t_end[idx], ref["t_end"])
     assert np.array_equal(res.status[idx], ref["status"]) and np.array_equal(res.nfe[idx], ref["nfe"])
     rt.close()
+
+
+def test_plasmasphere_jl_batch_bitexact():
+    """plasmasphere.jl functions on the GPU against the oracle, all three CA92 segments."""
+    rng = np.random.default_rng(7)
+    n = 4000
+    r = RE * rng.uniform(1.02, 9.5, n)
+    lam = np.deg2rad(rng.uniform(-70, 70, n))
+    rt = R.RayTracer("lat2d")
+    got = rt.plasmasphere(r, lam)
+    e = rt.env
+    L = O.lib()
+    Lref = np.array([L.orc_L_rlam(O._d(a), O._d(b), O._d(RE)) for a, b in zip(r, lam)])
+    eq = np.array([L.orc_plasmasphere_eq(O._d(x), O._d(e.Lppi), O._d(e.Lppo), O._d(0), O._d(90), O._d(2)) for x in Lref])
+    de = np.array([L.orc_diffusive_equilibrium(O._d(a), O._d(b)) for a, b in zip(r, eq)])
+    io = np.array([L.orc_ionosphere_eq(O._d(a), O._d(RE)) for a in r])
+    assert {0, 1, 2} <= set(np.digitize(Lref, [e.Lppi, e.Lppo]))
+    assert _same(got["L"], Lref) and _same(got["plasmasphere_eq"], eq)
+    assert _same(got["diffusive_equilibrium"], de) and _same(got["ionosphere_eq"], io) and _same(got["ne_total"], de + io)
+    rt.close()
+    rt3 = R.RayTracer("ray3d")
+    with pytest.raises(RuntimeError, match="RAY3D"):
+        rt3.plasmasphere(r[:4], lam[:4])
+    rt3.close()
