@@ -241,6 +241,19 @@ class RayTracer:
         _check(_lib().rt_plasmasphere_density(self._ctx, C.c_int64(n), _ptr(r), _ptr(lam), _ptr(out)), self._ctx)
         return dict(zip(("L", "plasmasphere_eq", "diffusive_equilibrium", "ionosphere_eq", "ne_total"), out))
 
+    def debug_rhs3d(self, u, freq):
+        """Diagnostics: both versions of the 3D right-hand side on chosen states u [n, 7] at frequency freq [n]:
+        returns (du_fast [n, 7], ok [n] bool — the branch-free code vouches for its result —, du_exact [n, 7])."""
+        u = np.ascontiguousarray(np.asarray(u, dtype=np.float64))
+        if u.ndim != 2 or u.shape[1] != 7:
+            raise ValueError("u must be [n, 7]")
+        n = u.shape[0]
+        inp = np.ascontiguousarray(np.concatenate([u, _f64(freq, n)[:, None]], axis=1))
+        df, de, ok = np.zeros((n, 7)), np.zeros((n, 7)), np.zeros(n, dtype=np.int32)
+        _check(_lib().rt_debug_rhs3d(self._ctx, C.c_int(n), _ptr(inp), _ptr(df), ok.ctypes.data_as(C.c_void_p), _ptr(de)),
+               self._ctx)
+        return df, ok.astype(bool), de
+
     # -- the solve ---------------------------------------------------------------------------------
     def solve(self, launch, with_trajectories=None):
         """Trace a launch list.  2D: columns (r, θ, χ, f, t) [5, n];  3D: (r, θ, ϕ, ρ_r, ρ_θ, ρ_ϕ, T0, f, t) [9, n]."""

@@ -87,8 +87,11 @@ struct RtVec7 { double v[7]; };
 struct RtVec4x { double v[4]; RtExtras2D ex; };
 
 // fallback census (cold path only): [0] calls, [1] r < 2^16 or negative, [2] non-finite input, [3] non-finite result,
-// [4] finite in and out (a guard was merely conservative), [5] 2D calls
+// [4] finite in and out (a guard was merely conservative), [5] 2D calls, [6] r is NaN, [7] |r| < 2^16
 __device__ unsigned long long rt_dbg_fallback[8];
+// the first RT_DBG_SAMPLES inputs (3D: u[0..6], freq) that took the exact path since the last reset
+#define RT_DBG_SAMPLES 8192
+__device__ double rt_dbg_sample[RT_DBG_SAMPLES][8];
 
 __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 y, double par) {
   RtVec7 d;
@@ -99,7 +102,14 @@ __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 
     fin_in = fin_in && rt_isfinite(y.v[c]);
     fin_out = fin_out && rt_isfinite(d.v[c]);
   }
-  atomicAdd(&rt_dbg_fallback[0], 1ULL);
+  const unsigned long long slot = atomicAdd(&rt_dbg_fallback[0], 1ULL);
+  if (slot < RT_DBG_SAMPLES) {
+#pragma unroll
+    for (int c = 0; c < 7; c++) rt_dbg_sample[slot][c] = y.v[c];
+    rt_dbg_sample[slot][7] = par;
+  }
+  if (y.v[0] != y.v[0]) atomicAdd(&rt_dbg_fallback[6], 1ULL);
+  else if (rt_abs(y.v[0]) < 65536.0) atomicAdd(&rt_dbg_fallback[7], 1ULL);
   if (!(y.v[0] >= 65536.0)) atomicAdd(&rt_dbg_fallback[1], 1ULL);
   else if (!fin_in) atomicAdd(&rt_dbg_fallback[2], 1ULL);
   else if (!fin_out) atomicAdd(&rt_dbg_fallback[3], 1ULL);
@@ -362,7 +372,7 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
     cnt = S.nsamp[i];
     status = S.status[i];
   }
-  bool running = valid && status == RT_RUNNING;
+  bool running = valid && status == RT_RUNNING, hit = false;
   RtExtras2D ex = {0, 0, 0, 0};
 
   for (int a = 0; a < attempts; a++) {
@@ -475,36 +485,10 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
     {  // re_cb: ContinuousCallback on u[1] - re
       double g0 = u[0] - E.re, g1 = un[0] - E.re;
       if ((g0 > 0.0 && g1 <= 0.0) || (g0 < 0.0 && g1 >= 0.0)) {
-        double lo = 0.0, hi = 1.0, b[7];
-        for (int it = 0; it < 52; it++) {
-          double mid = 0.5 * (lo + hi);
-          rt_dense_weights(mid, b);
-          double sacc = b[0] * RT_K(0, 0);
-#pragma unroll
-          for (int q = 1; q < 7; q++) sacc = sacc + b[q] * RT_K(q, 0);
-          double gm = (u[0] + h * sacc) - E.re;
-          bool same = (g0 > 0.0) ? (gm > 0.0) : (gm < 0.0);
-          if (same) lo = mid; else hi = mid;
-        }
-        rt_dense_weights(lo, b);
-#pragma unroll
-        for (int c = 0; c < DIM; c++) {
-          double sacc = b[0] * RT_K(0, c);
-#pragma unroll
-          for (int q = 1; q < 7; q++) sacc = sacc + b[q] * RT_K(q, c);
-          y[c] = u[c] + h * sacc;
-        }
-        t = t + lo * h;
-#pragma unroll
-        for (int c = 0; c < DIM; c++) u[c] = y[c];
-        status = RT_TERMINATED_EARTH;
+        // the ray stops here; the root is located after the loop, once per slice for all the lanes of the warp
+        // that hit the ground in it (inside the loop, lanes hitting in different attempts would serialise)
+        hit = true;
         running = false;
-        if (O.save_mode) {
-          if (MODE != RT_PRESET_RAY3D) {
-            rt_extras_at<(MODE == RT_PRESET_RAY3D) ? RT_PRESET_LAT2D : MODE>(E, u, &ex);
-          }
-          rt_traj_push<MODE>(S, O, i, cnt, t, u, ex, writer);
-        }
         continue;
       }
     }
@@ -524,6 +508,40 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
     }
     if (escaped) { status = RT_ESCAPED; running = false; continue; }
     h = hnew;
+  }
+
+  if (hit) {  // re_cb's root: bisection on the step's dense output (u, h and the seven stages are those of the step)
+    const double g0 = u[0] - E.re;
+    double lo = 0.0, hi = 1.0, b[7];
+    for (int it = 0; it < 52; it++) {
+      double mid = 0.5 * (lo + hi);
+      rt_dense_weights(mid, b);
+      double sacc = b[0] * RT_K(0, 0);
+#pragma unroll
+      for (int q = 1; q < 7; q++) sacc = sacc + b[q] * RT_K(q, 0);
+      double gm = (u[0] + h * sacc) - E.re;
+      bool same = (g0 > 0.0) ? (gm > 0.0) : (gm < 0.0);
+      if (same) lo = mid; else hi = mid;
+    }
+    rt_dense_weights(lo, b);
+#pragma unroll
+    for (int c = 0; c < DIM; c++) {
+      double sacc = b[0] * RT_K(0, c);
+#pragma unroll
+      for (int q = 1; q < 7; q++) sacc = sacc + b[q] * RT_K(q, c);
+      y[c] = u[c] + h * sacc;
+    }
+    t = t + lo * h;
+#pragma unroll
+    for (int c = 0; c < DIM; c++) u[c] = y[c];
+    status = RT_TERMINATED_EARTH;
+    running = false;
+    if (O.save_mode) {
+      if (MODE != RT_PRESET_RAY3D) {
+        rt_extras_at<(MODE == RT_PRESET_RAY3D) ? RT_PRESET_LAT2D : MODE>(E, u, &ex);
+      }
+      rt_traj_push<MODE>(S, O, i, cnt, t, u, ex, writer);
+    }
   }
 
   if (valid && writer) {

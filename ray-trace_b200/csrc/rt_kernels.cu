@@ -610,7 +610,9 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   S.traj = ctx->traj;
   cudaStream_t st = ctx->stream;
   const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
-  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static const int bulk_kb = getenv("RT_BULK_SMEM_KB") ? atoi(getenv("RT_BULK_SMEM_KB")) : 0;  // developer switch
+  const size_t smem_bulk = (size_t)bulk_kb * 1024 > smem ? (size_t)bulk_kb * 1024 : smem;
+  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bulk));
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
@@ -701,7 +703,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           else
-            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
+            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, (c == 0 && other.upper > 0) ? smem_bulk : smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           C.cur ^= 1;
@@ -911,6 +913,59 @@ extern "C" int rt_debug_fallback_counts(rt_ctx *ctx, unsigned long long *out8, i
     RT_CUDA(ctx, cudaMemcpyToSymbol(rt_dbg_fallback, z, sizeof(z)));
   }
   return RT_OK;
+}
+
+// Both versions of the 3D right-hand side on caller-chosen inputs (tests: wherever the branch-free one says its
+// result is exact, it has to have the exact one's bits, or NaN where that is NaN).  in[n][8] = u[0..6], freq.
+__global__ void rt_rhs3d_probe_kernel(const __grid_constant__ RtDevEnv E, int n, const double *in, double *du_fast,
+                                      int *ok, double *du_exact) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double u[7], df[7], de[7];
+  for (int c = 0; c < 7; c++) u[c] = in[(size_t)i * 8 + c];
+  const double f = in[(size_t)i * 8 + 7];
+  for (int c = 0; c < 7; c++) df[c] = 0.0;
+  ok[i] = rtf_haselgrove_3d<false>(E, u, f, df) ? 1 : 0;
+  rt_haselgrove_3d(E, u, f, de);
+  for (int c = 0; c < 7; c++) {
+    du_fast[(size_t)i * 7 + c] = df[c];
+    du_exact[(size_t)i * 7 + c] = de[c];
+  }
+}
+
+extern "C" int rt_debug_rhs3d(rt_ctx *ctx, int n, const double *in, double *du_fast, int *ok, double *du_exact) {
+  if (!ctx || n < 0 || !in || !du_fast || !ok || !du_exact) return set_err(ctx, RT_ERR_INVALID, "rt_debug_rhs3d: bad argument");
+  if (n == 0) return RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  double *d_in = nullptr, *d_f = nullptr, *d_e = nullptr;
+  int *d_ok = nullptr;
+  cudaError_t e = cudaMalloc(&d_in, (size_t)n * 8 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&d_f, (size_t)n * 7 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&d_e, (size_t)n * 7 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&d_ok, (size_t)n * sizeof(int));
+  if (e == cudaSuccess) e = cudaMemcpy(d_in, in, (size_t)n * 8 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    rt_rhs3d_probe_kernel<<<(n + 63) / 64, 64>>>(ctx->denv, n, d_in, d_f, d_ok, d_e);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(du_fast, d_f, (size_t)n * 7 * sizeof(double), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(du_exact, d_e, (size_t)n * 7 * sizeof(double), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(ok, d_ok, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost);
+  cudaFree(d_in);
+  cudaFree(d_f);
+  cudaFree(d_e);
+  cudaFree(d_ok);
+  if (e != cudaSuccess) return set_err(ctx, RT_ERR_CUDA, "rt_debug_rhs3d: %s", cudaGetErrorString(e));
+  return RT_OK;
+}
+
+// the inputs of the first exact-path calls since the last counter reset: out[max_rows][8] = u[0..6], freq (3D)
+extern "C" int rt_debug_fallback_samples(rt_ctx *ctx, double *out, int max_rows) {
+  if (!ctx || !out || max_rows < 0) return set_err(ctx, RT_ERR_INVALID, "rt_debug_fallback_samples: bad argument");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int rows = max_rows < RT_DBG_SAMPLES ? max_rows : RT_DBG_SAMPLES;
+  RT_CUDA(ctx, cudaMemcpyFromSymbol(out, rt_dbg_sample, (size_t)rows * 8 * sizeof(double)));
+  return rows;
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -40,22 +40,35 @@ RTF double rtf_div_c0(double a, double b, double y, bool &ok) {
 }
 
 // rt_density_cm3 without the ionosphere term's exp (hoisted: depends on r only)
-RTF double rtf_density_cm3(const RtDevEnv &E, double ne_iono, double L, bool &ok) {
+// ovf: the plasmasphere segment's 10^x overflows to +Inf for certain (x above rt_exp10's threshold, every input of
+// x computed exactly) -> the density is +Inf and the caller knows the right-hand side without the exact path
+RTF double rtf_density_cm3(const RtDevEnv &E, double ne_iono, double L, bool &ok, bool &ovf) {
   const bool seg1 = L <= E.Lppi;
   const bool seg2 = E.Lppi < L && L <= E.Lppo;
   const bool seg3 = E.Lppo < L;
   const double t2 = 2.0 - L;
   const double dsel = seg1 ? 1.5 : 10.0, ysel = seg1 ? E.y_1p5 : E.y_10;
-  bool oke = true;
-  double arg_e = rtf_div_c(t2, dsel, ysel, oke);
+  bool okd = true, okx = true;
+  double arg_e = rtf_div_c(t2, dsel, ysel, okd);
   arg_e = seg2 ? 0.0 : arg_e;  // unused by segment 2
-  double ex = rtf_exp(arg_e, oke);
-  ok = ok && (oke || seg2);
+  double ex = rtf_exp(arg_e, okx);
+  // exp's argument beyond the branch-free range, where the exact value is not needed:
+  //  trough, arg <= -700 (L > 7002, near the poles): 0 <= exp < 2^-1000 and its only use is 1.0 - exp == 1.0;
+  //  plasmasphere, arg >= 700 (L < -1048): exp >= 1e304 or +Inf, so with ca_coef >= 1e-200 the exponent of 10
+  //  is >= 1e104 (its other term is positive for negative L) and 10^x = +Inf for certain
+  // (integer tests on the high word: FP64 compares cost pipe slots)
+  const int arg_hi = __double2hiint(arg_e);  // 700.0 = 0x4085E000'00000000; arg_e is finite when okd
+  const bool tiny = seg3 && okd && ((unsigned)arg_hi >= 0xC085E000u);
+  const bool huge = seg1 && okd && (arg_hi >= 0x4085E000) && (E.ca_coef >= 1e-200);
+  ex = tiny ? 0.0 : ex;
+  ok = ok && ((okd && (okx || tiny || huge)) || seg2);
   double a1 = (-0.3145 * L + 3.9043) + E.ca_coef * ex;
   bool ok2 = true;
   double a2 = rtf_div_c(E.Lppi - L, 0.1, E.y_0p1, ok2);
   ok = ok && (ok2 || !seg2);
   double arg10 = seg1 ? a1 : (seg2 ? a2 : 0.0);
+  // rt_exp10 returns +Inf above 308.2547...; 308.5 has a round high word (arg10 is finite or +Inf here)
+  ovf = ok && seg1 && (huge || __double2hiint(arg10) >= 0x40734800);
   double p10 = rtf_exp10(arg10, ok);
   bool ok3 = true;
   double pw = rtf_pow_m4p5(seg3 ? L : 1.0, ok3);
@@ -127,6 +140,7 @@ RTF RtMu rtf_stix(const RtPlasma &p, double omega, bool &ok) {
 struct RtRad3D {  // shared by the three theta points of one right-hand side
   double bq2, bq;  // (-2 B0) (re/r)^3, B0 (re/r)^3
   double ne_iono, mumag, yr;
+  bool iono_ovf;
 };
 
 RTF void rtf_rad3d(const RtDevEnv &E, double r, double rho_r, double rho_t, double rho_p, RtRad3D &R, bool &ok) {
@@ -136,13 +150,17 @@ RTF void rtf_rad3d(const RtDevEnv &E, double r, double rho_r, double rho_t, doub
   R.bq2 = (-2.0 * E.B0) * q3;
   R.bq = E.B0 * q3;
   const double rE = rtf_div_c(r, E.re, E.y_re, ok);
-  R.ne_iono = E.iono_n0 * rtf_exp(E.iono_k * (rE - E.iono_h), ok);
+  const double arg_i = E.iono_k * (rE - E.iono_h);
+  // far below the centre (r < -1e9 m) the ionosphere's exp overflows: rt_exp returns +Inf above 709.78 (712 has a
+  // round high word), the density is +-Inf or NaN whatever the plasmasphere term is, and mu is NaN (see below)
+  R.iono_ovf = ok && (__double2hiint(arg_i) >= 0x40864000);
+  R.ne_iono = E.iono_n0 * rtf_exp(arg_i, ok);
   R.mumag = rtf_sqrt((rho_r * rho_r + rho_t * rho_t) + rho_p * rho_p, ok);
 }
 
 // rt_geo3d at colatitude th (B_phi = 0: its products are +-0 and drop out for finite rho_phi)
 RTF void rtf_geo3d(const RtDevEnv &E, const RtRad3D &R, double r, double th, double rho_r, double rho_t, RtGeo3D &g,
-                   bool &ok) {
+                   bool &ok, bool &ovf) {
   const double lam = RT_PI / 2.0 - th;
   double sl, cl;
   rtf_sincos(lam, &sl, &cl, ok);
@@ -152,7 +170,7 @@ RTF void rtf_geo3d(const RtDevEnv &E, const RtRad3D &R, double r, double th, dou
   g.Bp = 0.0;
   g.Bmag = rtf_sqrt(g.Br * g.Br + g.Bt * g.Bt, ok);
   const double L = rtf_div(r, E.re * (cl * cl), ok);
-  const double n_e = rtf_density_cm3(E, R.ne_iono, L, ok) * 1e6;
+  const double n_e = rtf_density_cm3(E, R.ne_iono, L, ok, ovf) * 1e6;
   const double dot = g.Br * rho_r + g.Bt * rho_t;
   const double cos_psi = rtf_div(dot, g.Bmag * R.mumag, ok);
   g.psi = rtf_acos(cos_psi, ok);
@@ -198,6 +216,17 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
   // negative radii routinely); rho_phi finite, non-zero
   ok = ok && ((unsigned)((__double2hiint(r) & 0x7fffffff) - 0x40f00000) < (0x60000000u - 0x40f00000u));
   ok = ok && rtf_quarter_range(rp_);
+  // Two inputs whose result is known without arithmetic — all seven derivatives NaN — and which the garbage trial
+  // stages of a step about to be rejected hit often enough to matter (one lane on the exact path stalls its warp
+  // for ~10 right-hand sides):
+  //  (1) r is NaN: |B| is NaN, so is every Stix parameter and mu, and every derivative has mu as a factor;
+  //  (2) the centre density is +-Inf or NaN (negative radius: the plasmasphere's 10^x overflows for L < -11, the
+  //      ionosphere's exp for r < -1e9 m): X_e and X_p are +-Inf or NaN, so P is +-Inf or NaN and R, L are each +-Inf or NaN whatever the
+  //      gyrofrequency terms are; then either S or D is NaN (Inf - Inf), A = S s^2 + P c^2 or F^2 (through P D) is NaN,
+  //      mu = sqrt|(B + F) / 2A| is NaN, and again every derivative has mu as a factor.
+  // (NaN payloads never reach a result: the step is rejected on EEst != EEst.)
+  const bool nan_in = (unsigned)(__double2hiint(r) & 0x7fffffff) > 0x7ff00000u;  // any quiet NaN
+  bool ovf_c = false, ovf_x = false;
   const double two_pi = 2.0 * RT_PI;
   RtRad3D Rd;
   rtf_rad3d(E, r, rr_, rt_, rp_, Rd, ok);
@@ -210,7 +239,8 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
     const int k = rt_group_rank();
     const double th_k = (k == 1) ? th - 1.0e-11 / 2.0 : ((k == 2) ? th + 1.0e-11 / 2.0 : th);
     RtGeo3D g;
-    rtf_geo3d(E, Rd, r, th_k, rr_, rt_, g, ok);
+    rtf_geo3d(E, Rd, r, th_k, rr_, rt_, g, ok, ovf_x);
+    ovf_c = __shfl_sync(rt_group_mask(), ovf_x ? 1 : 0, rt_group_base()) != 0;
     RtMu v = rtf_stix<true>(g.p, two_pi * freq, ok);
     gc.Br = rt_group_get(g.Br, 0);
     gc.Bt = rt_group_get(g.Bt, 0);
@@ -232,13 +262,13 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
   } else {
     // centre first (with d(mu)/d(psi)); the theta -/+ and f -/+ pairs are loops so that the build can choose
     // between rolled (small register footprint, more resident warps) and unrolled (more chains per warp)
-    rtf_geo3d(E, Rd, r, th, rr_, rt_, gc, ok);
+    rtf_geo3d(E, Rd, r, th, rr_, rt_, gc, ok, ovf_c);
     c = rtf_stix<true>(gc.p, two_pi * freq, ok);
     double mt[2], mf[2];
     RT_PAIR_LOOP
     for (int k = 0; k < 2; k++) {
       RtGeo3D g;
-      rtf_geo3d(E, Rd, r, k ? th + 1.0e-11 / 2.0 : th - 1.0e-11 / 2.0, rr_, rt_, g, ok);
+      rtf_geo3d(E, Rd, r, k ? th + 1.0e-11 / 2.0 : th - 1.0e-11 / 2.0, rr_, rt_, g, ok, ovf_x);
       const double m = rtf_stix<false>(g.p, two_pi * freq, ok).mu;
       if (k == 0) mt[0] = m; else mt[1] = m;
     }
@@ -253,9 +283,13 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
     mu_fr = mf[1];
   }
   ok = ok && rtf_quarter_range(gc.Bmag);
+  // known NaN result: poison mu; rtf_tail3d is arithmetic and divisions only, every derivative has mu as a factor
+  // (its flags fail on the way: the return value below overrides them)
+  const bool known_nan = nan_in || ovf_c || Rd.iono_ovf;  // the same on the lanes of a group
+  c.mu = known_nan ? rt_nan() : c.mu;
   rtf_tail3d(E, Rd, u, freq, gc, c.mu, c.dmudpsi, mu_tl, mu_tr, mu_fl, mu_fr, du, ok);
   if (COOP) ok = rt_group_all(ok);
-  return ok;
+  return ok || known_nan;
 }
 
 // =====================================================================================================
@@ -293,7 +327,8 @@ RTF void rtf_geo2d_lat(const RtDevEnv &E, const RtRad2D &R, double r, double th,
   psi = (RT_PI / 2.0 + dip) + chi;
   const double Bmag = R.bq * rtf_sqrt(1.0 + (3.0 * st) * st, ok);
   const double Lshell = rtf_div(r, E.re * (ct * ct), ok);
-  const double n_e = rtf_density_cm3(E, R.ne_iono, Lshell, ok) * 1e6;
+  bool ovf_unused;
+  const double n_e = rtf_density_cm3(E, R.ne_iono, Lshell, ok, ovf_unused) * 1e6;
   rtf_plasma_from(E, n_e, Bmag, p, ok);
   rtf_sincos(psi, &p.s, &p.c, ok);
 }

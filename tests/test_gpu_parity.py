@@ -183,6 +183,33 @@ def test_branch_free_primitives_bit_equal_exact_ones():
         assert compared > 5_000_000 and mism == 0, (k, compared, mism, flagged)
 
 
+def test_branch_free_rhs_vouches_only_for_exact_bits_on_wild_states():
+    """The trial stages of steps about to be rejected land anywhere (negative radii, L < -1000, poles): wherever
+    the branch-free right-hand side says its result is exact it has the exact code's bits — or is NaN where the
+    exact result is NaN in all seven components (the known-NaN shortcuts of rtf_haselgrove_3d)."""
+    rng = np.random.default_rng(11)
+    n = 300_000
+    sign = np.where(rng.random(n) < 0.6, -1.0, 1.0)
+    r = sign * 10.0 ** rng.uniform(4.0, 11.5, n)
+    th = np.where(rng.random(n) < 0.5, rng.uniform(0, np.pi, n), rng.normal(0, 300, n))
+    th[: n // 20] = rng.choice([0.0, np.pi, 1e-9, np.pi - 1e-9, 3.1147], n // 20)  # poles
+    rho = rng.normal(0, 1, (n, 3)) * 10.0 ** rng.uniform(-2, 5, (n, 1))
+    u = np.column_stack([r, th, rng.uniform(-3, 3, n), rho, rng.uniform(0, 1, n)])
+    u[:100, 0] = np.nan
+    u[100:200, 0] = np.inf
+    u[200:300, 5] = 0.0
+    f = rng.choice([1000.0, 5000.0, 25000.0], n)
+    rt = R.RayTracer("ray3d")
+    df, ok, de = rt.debug_rhs3d(u, f)
+    rt.close()
+    nan_e = np.isnan(de).all(axis=1)
+    same = (df.view(np.uint64) == de.view(np.uint64)).all(axis=1) | (np.isnan(df).all(axis=1) & nan_e)
+    assert not (ok & ~same).any(), (int((ok & ~same).sum()), u[ok & ~same][:3])
+    # the shortcuts are exercised, and most wild states stay off the exact path
+    assert (ok & nan_e).sum() > 20_000 and ok.mean() > 0.6, (int((ok & nan_e).sum()), float(ok.mean()))
+    assert ok[:100].all() and nan_e[:100].all()  # NaN radius
+
+
 def test_two_chains_and_one_chain_give_identical_results():
     """Rays that start upward go to the priority chain (scheduling only)."""
     launch = sweeps.sweep_3d(12, 3, 24)
