@@ -19,7 +19,9 @@
 #pragma once
 #include "rt_physics_fast.cuh"
 
+#ifndef RT_BLOCK
 #define RT_BLOCK 128
+#endif
 #ifndef RT_COOP_MINBLOCKS
 #define RT_COOP_MINBLOCKS 1
 #endif

@@ -683,18 +683,24 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         }
       }
       if (!C.pending && C.upper > 0) {
-        // 3 lanes per ray (rt_physics.cuh) buys latency (0.45x per right-hand side) with throughput (1.4x the issue
-        // slots): used once a chain is down to its long rays AND the two chains together no longer fill the GPU
-        // (measured: 25 us per attempt with 7 k rays on the GPU, 35 us with 14 k, 60 us with 27 k;
-        // tools/gpu_coop_density.py).  RT_COOP_POLICY=0 (developer switch) drops the second condition.
+        // 3 lanes per ray (rt_physics.cuh) buys latency (19 us per attempt instead of 32 with the GPU to itself)
+        // with throughput: a cooperative block holds 40 rays in the registers of 128, and next to full lists it was
+        // measured to cost 2.7x the SM time per attempt of one thread per ray (profiles/r1_schedule_experiments.md),
+        // which is exactly what it saves at the end -- so it is used once a chain is down to its long rays AND the
+        // two chains together leave SMs idle (<= 35 k rays, i.e. 270 of the 444 resident blocks).
+        // RT_COOP_POLICY=0 (developer switch) drops the second condition.
         const Chain &other = ch[c ^ 1];
         static const int policy = getenv("RT_COOP_POLICY") ? atoi(getenv("RT_COOP_POLICY")) : 1;
-        const bool coop = C.upper <= coop_threshold && (policy == 0 || C.upper + other.upper <= coop_threshold + 2048);
+        static const long long coop_sum = getenv("RT_COOP_SUM") ? atoll(getenv("RT_COOP_SUM")) : 25000;
+        const bool coop = C.upper <= coop_threshold && (policy == 0 || C.upper + other.upper <= coop_threshold + coop_sum);
         // a launch of the priority chain has to wait for blocks of the other chain to retire before it gets SM
         // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
         static const int coop_att = getenv("RT_COOP_ATT") ? atoi(getenv("RT_COOP_ATT")) : 32;
-        const int batch = coop ? 4 : 8;
         const int att = coop ? (C.att > coop_att ? C.att : coop_att) : C.att;
+        // a short list still on one thread per ray is waiting for the other chain to drain: keep its batches short
+        // (<= 64 attempts) so that the switch to 3 lanes per ray is not delayed by a batch already enqueued
+        static const int wait_att = getenv("RT_WAIT_ATT") ? atoi(getenv("RT_WAIT_ATT")) : 64;
+        const int batch = coop ? 4 : ((C.upper <= coop_threshold && att * 8 > wait_att) ? (wait_att / att > 1 ? wait_att / att : 1) : 8);
         C.nominal += (long long)att * batch;
         for (int b = 0; b < batch; b++, C.k++) {
           const int k = C.k;

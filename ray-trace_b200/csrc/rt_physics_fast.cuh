@@ -24,6 +24,15 @@
 #else
 #define RT_PAIR_LOOP _Pragma("unroll")
 #endif
+// the f -/+ pair alone (two Stix evaluations on the same medium, few live values) can be unrolled separately
+#ifndef RT_ROLL_F
+#define RT_ROLL_F RT_ROLL
+#endif
+#if RT_ROLL_F
+#define RT_PAIR_LOOP_F _Pragma("unroll 1")
+#else
+#define RT_PAIR_LOOP_F _Pragma("unroll")
+#endif
 
 // exponent field of x in [0x200, 0x5ff]: products of two such numbers neither vanish nor become NaN
 RTF bool rtf_quarter_range(double x) {
@@ -272,7 +281,7 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
       const double m = rtf_stix<false>(g.p, two_pi * freq, ok).mu;
       if (k == 0) mt[0] = m; else mt[1] = m;
     }
-    RT_PAIR_LOOP
+    RT_PAIR_LOOP_F
     for (int k = 0; k < 2; k++) {
       const double m = rtf_stix<false>(gc.p, two_pi * (k ? freq + 1.0e-5 / 2.0 : freq - 1.0e-5 / 2.0), ok).mu;
       if (k == 0) mf[0] = m; else mf[1] = m;
@@ -378,7 +387,7 @@ RTF bool rtf_haselgrove_2d_lat(const RtDevEnv &E, const double *u, double *du, R
       const double m = rtf_stix<false>(p, two_pi * freq, ok).mu;
       if (k == 0) mt[0] = m; else mt[1] = m;
     }
-    RT_PAIR_LOOP
+    RT_PAIR_LOOP_F
     for (int k = 0; k < 2; k++) {
       const double m = rtf_stix<false>(pc, two_pi * (k ? freq + 1.0e-5 / 2.0 : freq - 1.0e-5 / 2.0), ok).mu;
       if (k == 0) mf[0] = m; else mf[1] = m;

@@ -11,7 +11,7 @@ res = rt.solve(full)
 long_idx = np.nonzero(res.naccept + res.nreject > 1000)[0]
 print("long rays:", long_idx.size, flush=True)
 base = full[:, long_idx]
-for mult in (1, 2, 4, 6):
+for mult in (1, 2, 3):
     launch = np.ascontiguousarray(np.tile(base, (1, mult)))
     for coop in (10**9, -1):
         rt.set_solver(r_esc=10 * RE, coop_threshold=coop, single_chain=1)
