@@ -31,9 +31,11 @@ struct rt_ctx {
   int cap_dim = 0;
   double *k1 = nullptr, *h = nullptr, *qold = nullptr, *par = nullptr;
   int *sgn = nullptr, *nsamp = nullptr, *idx[2] = {nullptr, nullptr}, *count = nullptr;
-  int *idx_prio[2] = {nullptr, nullptr};  // work lists of the priority chain (count + 4 .. count + 6 are its counters)
+  int *idx_prio[2] = {nullptr, nullptr};  // work lists of the priority chains (chain c's counters: count + 4 c .. + 2)
   cudaStream_t prio_stream = nullptr;     // high-priority stream of the priority chain
-  cudaEvent_t ev_chain[2] = {nullptr, nullptr}, ev_fork = nullptr, ev_join = nullptr;
+  cudaStream_t aux_stream[2] = {nullptr, nullptr};  // second halves of the normal / priority list (chains 2 / 3)
+  cudaEvent_t ev_chain[4] = {nullptr, nullptr, nullptr, nullptr}, ev_fork = nullptr;
+  cudaEvent_t ev_join[3] = {nullptr, nullptr, nullptr};
   double *traj = nullptr;
   size_t traj_bytes = 0;
   int *h_count = nullptr;  // pinned
@@ -250,15 +252,17 @@ extern "C" int rt_create(rt_ctx **out, int device) {
   RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
   ctx->stream = ctx->own_stream;
   for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&ctx->ev[k]));
-  RT_CUDA(ctx, cudaMallocHost(&ctx->h_count, 4 * sizeof(int)));
-  RT_CUDA(ctx, cudaMalloc(&ctx->count, 8 * sizeof(int)));
+  RT_CUDA(ctx, cudaMallocHost(&ctx->h_count, 16 * sizeof(int)));
+  RT_CUDA(ctx, cudaMalloc(&ctx->count, 16 * sizeof(int)));
   {
     int lo = 0, hi = 0;
     RT_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
     RT_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->prio_stream, cudaStreamNonBlocking, hi));
-    for (int k = 0; k < 2; k++) RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_chain[k], cudaEventDisableTiming));
+    RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->aux_stream[0], cudaStreamNonBlocking));
+    RT_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->aux_stream[1], cudaStreamNonBlocking, hi));
+    for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_chain[k], cudaEventDisableTiming));
     RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
-    RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    for (int k = 0; k < 3; k++) RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming));
   }
   rt_env_preset(RT_PRESET_LAT2D, &ctx->env);
   rt_solver_preset(RT_PRESET_LAT2D, &ctx->opts);
@@ -302,11 +306,14 @@ extern "C" void rt_destroy(rt_ctx *ctx) {
   cudaFreeHost(ctx->h_count);
   for (int k = 0; k < 4; k++)
     if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
-  for (int k = 0; k < 2; k++)
+  for (int k = 0; k < 4; k++)
     if (ctx->ev_chain[k]) cudaEventDestroy(ctx->ev_chain[k]);
   if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
-  if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+  for (int k = 0; k < 3; k++)
+    if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]);
   if (ctx->prio_stream) cudaStreamDestroy(ctx->prio_stream);
+  for (int k = 0; k < 2; k++)
+    if (ctx->aux_stream[k]) cudaStreamDestroy(ctx->aux_stream[k]);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -610,9 +617,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   S.traj = ctx->traj;
   cudaStream_t st = ctx->stream;
   const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
-  static const int bulk_kb = getenv("RT_BULK_SMEM_KB") ? atoi(getenv("RT_BULK_SMEM_KB")) : 0;  // developer switch
-  const size_t smem_bulk = (size_t)bulk_kb * 1024 > smem ? (size_t)bulk_kb * 1024 : smem;
-  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bulk));
+  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
@@ -620,7 +625,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   const bool two_chains = ctx->opts.single_chain == 0;
   ctx->stats = rt_stats{};
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
-  RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, 8 * sizeof(int), st));
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->count, 0, 16 * sizeof(int), st));
   rt_init_kernel<MODE><<<grid_for(n, RT_BLOCK), RT_BLOCK, 0, st>>>(ctx->denv, O, S, L, ctx->idx[0], ctx->count,
                                                                   two_chains ? ctx->idx_prio[0] : nullptr,
                                                                   ctx->count + 4);
@@ -629,13 +634,15 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
   RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count, ctx->count, sizeof(int), cudaMemcpyDeviceToHost, st));
   RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count + 1, ctx->count + 4, sizeof(int), cudaMemcpyDeviceToHost, st));
-  RT_CUDA(ctx, cudaEventRecord(ctx->ev_fork, st));
   RT_CUDA(ctx, cudaStreamSynchronize(st));
-  // Two independent chains of slices: chain 0 (normal list) on the caller's stream, chain 1 (priority list:
-  // rays that start upward, see rt_init_kernel) on the context's high-priority stream.  Within a chain, launch k
-  // reads counter k%3, appends survivors to counter (k+1)%3 and clears (k+2)%3, so a batch of slices needs no
-  // host round trip; after each batch the host reads the live count (an upper bound for the next batch's grid:
-  // a list only shrinks).  The host polls the two chains' events and feeds whichever is idle.
+  // Independent chains of slices.  Chain 0: the normal list, on the caller's stream; chain 1: the priority list
+  // (rays that start upward, see rt_init_kernel), on a high-priority stream.  A list of more than a wave or so is
+  // cut in two halves that run as separate chains (2: second half of the normal list, 3: of the priority list) so
+  // that the partial last wave of one launch is filled by the other chain's blocks (100 k rays are 782 blocks on
+  // 444 resident ones: 1.76 waves per launch by themselves).  Within a chain, launch k reads counter k%3, appends
+  // survivors to counter (k+1)%3 and clears (k+2)%3, so a batch of slices needs no host round trip; after each
+  // batch the host reads the live count (an upper bound for the next batch's grid: a list only shrinks).  The
+  // host polls the chains' events and feeds whichever is idle.
   struct Chain {
     cudaStream_t st;
     int *idx[2];
@@ -647,21 +654,46 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
     bool pending;
     int att;            // attempts per launch of the next batch (adaptive, see below)
     long long nominal;  // attempts enqueued so far (diagnostics)
-  } ch[2] = {{st, {ctx->idx[0], ctx->idx[1]}, ctx->count, ctx->h_count + 2, ctx->ev_chain[0], ctx->h_count[0], 0, 0, false,
-              attempts, 0},
-             {ctx->prio_stream, {ctx->idx_prio[0], ctx->idx_prio[1]}, ctx->count + 4, ctx->h_count + 3, ctx->ev_chain[1],
-              ctx->h_count[1], 0, 0, false, attempts, 0}};
+  } ch[4];
+  static const long long split_min = getenv("RT_SPLIT_MIN") ? atoll(getenv("RT_SPLIT_MIN")) : 32768;
+  {
+    cudaStream_t streams[4] = {st, ctx->prio_stream, ctx->aux_stream[0], ctx->aux_stream[1]};
+    int *h_init = ctx->h_count + 8;  // first counters of the four chains, uploaded below when a list is cut
+    bool cut = false;
+    for (int c = 0; c < 2; c++) {
+      int *const *base = c ? ctx->idx_prio : ctx->idx;
+      const long long total = ctx->h_count[c];
+      long long half = total;
+      if (two_chains && total >= split_min) half = ((total / 2 + RT_BLOCK - 1) / RT_BLOCK) * RT_BLOCK;
+      cut = cut || half < total;
+      for (int part = 0; part < 2; part++) {
+        const int id = c + 2 * part;
+        const long long off = part ? half : 0;
+        ch[id] = Chain{streams[id], {base[0] ? base[0] + off : nullptr, base[1] ? base[1] + off : nullptr},
+                       ctx->count + 4 * id, ctx->h_count + 4 + id, ctx->ev_chain[id],
+                       part ? total - half : half, 0, 0, false, attempts, 0};
+        h_init[id] = (int)ch[id].upper;
+      }
+    }
+    if (cut)
+      for (int id = 0; id < 4; id++)
+        RT_CUDA(ctx, cudaMemcpyAsync(ctx->count + 4 * id, h_init + id, sizeof(int), cudaMemcpyHostToDevice, st));
+  }
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev_fork, st));
   // Slice length adapts when the caller did not fix it: a batch that lost fewer than 3 % of its rays doubles the
   // next batch's attempts per launch (up to 64) — lists of long-lived rays (iteration-capped 2D sweeps, the
   // magnetospheric paths) need no compaction, and fewer launches mean fewer waits for SM slots; any batch that
   // does lose rays falls back to the base length.
   const bool adapt = ctx->opts.slice_attempts <= 0;
-  ctx->stats.prio_rays = ch[1].upper;
-  if (ch[1].upper > 0) RT_CUDA(ctx, cudaStreamWaitEvent(ch[1].st, ctx->ev_fork, 0));
+  ctx->stats.prio_rays = ch[1].upper + ch[3].upper;
+  for (int c = 1; c < 4; c++)
+    if (ch[c].upper > 0) RT_CUDA(ctx, cudaStreamWaitEvent(ch[c].st, ctx->ev_fork, 0));
   const bool dbg = getenv("RT_DEBUG") != nullptr;
+  const int order[4] = {1, 3, 0, 2};  // priority chains first
   for (;;) {
-    bool any = false;
-    for (int c = 1; c >= 0; c--) {  // priority chain first
+    int npending = 0, nactive = 0, last_pending = -1;
+    for (int oi = 0; oi < 4; oi++) {
+      const int c = order[oi];
       Chain &C = ch[c];
       if (C.pending) {
         cudaError_t q = cudaEventQuery(C.ev);
@@ -686,18 +718,18 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         // 3 lanes per ray (rt_physics.cuh) buys latency (19 us per attempt instead of 32 with the GPU to itself)
         // with throughput: a cooperative block holds 40 rays in the registers of 128, and next to full lists it was
         // measured to cost 2.7x the SM time per attempt of one thread per ray (profiles/r1_schedule_experiments.md),
-        // which is exactly what it saves at the end -- so it is used once a chain is down to its long rays AND the
-        // two chains together leave SMs idle (<= 35 k rays, i.e. 270 of the 444 resident blocks).
+        // which is exactly what it saves at the end -- so it is used once a chain is down to its long rays AND all
+        // chains together leave SMs idle (<= 35 k rays, i.e. 270 of the 444 resident blocks).
         // RT_COOP_POLICY=0 (developer switch) drops the second condition.
-        const Chain &other = ch[c ^ 1];
+        const long long all = ch[0].upper + ch[1].upper + ch[2].upper + ch[3].upper;
         static const int policy = getenv("RT_COOP_POLICY") ? atoi(getenv("RT_COOP_POLICY")) : 1;
         static const long long coop_sum = getenv("RT_COOP_SUM") ? atoll(getenv("RT_COOP_SUM")) : 25000;
-        const bool coop = C.upper <= coop_threshold && (policy == 0 || C.upper + other.upper <= coop_threshold + coop_sum);
+        const bool coop = C.upper <= coop_threshold && (policy == 0 || all <= coop_threshold + coop_sum);
         // a launch of the priority chain has to wait for blocks of the other chain to retire before it gets SM
         // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
         static const int coop_att = getenv("RT_COOP_ATT") ? atoi(getenv("RT_COOP_ATT")) : 32;
         const int att = coop ? (C.att > coop_att ? C.att : coop_att) : C.att;
-        // a short list still on one thread per ray is waiting for the other chain to drain: keep its batches short
+        // a short list still on one thread per ray is waiting for the other chains to drain: keep its batches short
         // (<= 64 attempts) so that the switch to 3 lanes per ray is not delayed by a batch already enqueued
         static const int wait_att = getenv("RT_WAIT_ATT") ? atoi(getenv("RT_WAIT_ATT")) : 64;
         const int batch = coop ? 4 : ((C.upper <= coop_threshold && att * 8 > wait_att) ? (wait_att / att > 1 ? wait_att / att : 1) : 8);
@@ -709,7 +741,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           else
-            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, (c == 0 && other.upper > 0) ? smem_bulk : smem, C.st>>>(
+            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           C.cur ^= 1;
@@ -721,21 +753,23 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         RT_CUDA(ctx, cudaEventRecord(C.ev, C.st));
         C.pending = true;
       }
-      any = any || C.pending;
+      if (C.pending) {
+        npending++;
+        last_pending = c;
+      }
+      if (C.pending || C.upper > 0) nactive++;
     }
-    if (!any) break;
-    if (ch[0].pending && ch[1].pending) {  // both busy: block on the one that is ahead in the queue instead of spinning hot
-      std::this_thread::yield();
-    } else if (ch[0].pending && ch[1].upper <= 0) {
-      cudaEventSynchronize(ch[0].ev);
-    } else if (ch[1].pending && ch[0].upper <= 0) {
-      cudaEventSynchronize(ch[1].ev);
+    if (npending == 0) break;
+    if (nactive == 1)
+      cudaEventSynchronize(ch[last_pending].ev);  // one chain left: block on it
+    else
+      std::this_thread::yield();  // several busy: poll
+  }
+  for (int c = 1; c < 4; c++)
+    if (ch[c].k > 0) {  // join the other streams back into the caller's stream
+      RT_CUDA(ctx, cudaEventRecord(ctx->ev_join[c - 1], ch[c].st));
+      RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_join[c - 1], 0));
     }
-  }
-  if (ch[1].k > 0) {  // join the priority stream back into the caller's stream
-    RT_CUDA(ctx, cudaEventRecord(ctx->ev_join, ch[1].st));
-    RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_join, 0));
-  }
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
   rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, R.u_end + (size_t)(DIM - 1) * n, ctx->par,
                                                           MODE == RT_PRESET_RAY3D, R.group_delay);
