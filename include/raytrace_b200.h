@@ -166,6 +166,13 @@ RT_API int rt_traj_columns(const rt_ctx *ctx);
 RT_API int rt_traj_size(rt_ctx *ctx, int64_t *total_samples);
 /* offsets[n+1] (CSR), samples[total][columns] row-major */
 RT_API int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples);
+/* what the reference derives from a trajectory after the solve, computed on the device and packed with the same
+ * offsets (as returned by rt_traj_copy): 2D  x, y, dt  with x = r cos(lam), y = r sin(lam) (RayTrace_lat.jl:351-352;
+ * colatitude presets x = r sin(th), y = r cos(th): RayMain.jl:400-401, scratch.jl:407-408) and
+ * dt[i] = t[i+1] - t[i], last 0 (RayTrace_lat.jl:369-372) = 3 columns;
+ * 3D  x, y, z, dt  with the spherical-to-Cartesian map of (r, th, ph) = 4 columns */
+RT_API int rt_traj_derived_columns(rt_ctx *ctx);
+RT_API int rt_traj_derived(rt_ctx *ctx, const int64_t *offsets, double *out);
 
 /* ---- instrumentation ------------------------------------------------------------------------- */
 typedef struct rt_stats {

@@ -135,10 +135,16 @@ class SolveResult:
         self.nreflect = np.zeros(n, np.int32)
         self.traj_offsets = None
         self.traj = None
+        self.traj_derived = None
         self.stats = None
 
     def _c(self):
         return _Result(*[_ptr(getattr(self, k)) for k, _ in _Result._fields_])
+
+    def derived(self, i):
+        """Rows (x, y, dt) — 3D: (x, y, z, dt) — of ray i's trajectory (RayTracer.solve(..., derived=True))."""
+        lo, hi = self.traj_offsets[i], self.traj_offsets[i + 1]
+        return self.traj_derived[lo:hi]
 
     def trajectory(self, i):
         """Rows (t, u..., [mu, dmudpsi, dip, psi]) of ray i — sol.t / sol[k,:] / saved_mu."""
@@ -255,7 +261,7 @@ class RayTracer:
         return df, ok.astype(bool), de
 
     # -- the solve ---------------------------------------------------------------------------------
-    def solve(self, launch, with_trajectories=None):
+    def solve(self, launch, with_trajectories=None, derived=False):
         """Trace a launch list.  2D: columns (r, θ, χ, f, t) [5, n];  3D: (r, θ, ϕ, ρ_r, ρ_θ, ρ_ϕ, T0, f, t) [9, n]."""
         launch = np.ascontiguousarray(np.asarray(launch, dtype=np.float64))
         ncol = 9 if self.dim == 7 else 5
@@ -276,6 +282,9 @@ class RayTracer:
             res.traj_offsets = np.zeros(n + 1, np.int64)
             res.traj = np.zeros((total.value, ncolt))
             _check(_lib().rt_traj_copy(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj)), self._ctx)
+            if derived:  # Cartesian track and step sizes, computed on the device (RayTrace_lat.jl:351-352,369-372)
+                res.traj_derived = np.zeros((total.value, _lib().rt_traj_derived_columns(self._ctx)))
+                _check(_lib().rt_traj_derived(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj_derived)), self._ctx)
         return res
 
 

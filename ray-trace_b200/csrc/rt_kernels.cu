@@ -943,6 +943,73 @@ extern "C" int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples) {
   return RT_OK;
 }
 
+// Post-processing of the saved trajectories on the device: the Cartesian track and the step-size
+// series the reference derives after a solve — x = r cos(lambda), y = r sin(lambda) (RayTrace_lat.jl:351-352;
+// colatitude presets: x = r sin(theta), y = r cos(theta), RayMain.jl:400-401, scratch.jl:407-408),
+// dt[i] = t[i+1] - t[i] with a trailing 0 (RayTrace_lat.jl:369-372).  3D [EXT]: x = r sin(theta) cos(phi),
+// y = r sin(theta) sin(phi), z = r cos(theta).  Packed like rt_traj_copy: out[offsets[ray] + k][3 or 4].
+__global__ void rt_traj_derived_kernel(long long n, int cap, int ncol, int mode, const double *traj,
+                                       const long long *offsets, double *out) {
+  const long long ray = blockIdx.x;
+  const long long lo = offsets[ray], cnt = offsets[ray + 1] - lo;
+  const double *src = traj + (size_t)ray * cap * ncol;
+  const int nd = (mode == RT_PRESET_RAY3D) ? 4 : 3;
+  for (long long k = threadIdx.x; k < cnt; k += blockDim.x) {
+    const double *row = src + (size_t)k * ncol;
+    const double t = row[0], r = row[1], a = row[2];
+    double *o = out + (size_t)(lo + k) * nd;
+    double sa, ca;
+    rt_sincos(a, &sa, &ca);
+    if (mode == RT_PRESET_RAY3D) {
+      double sp, cp;
+      rt_sincos(row[3], &sp, &cp);
+      o[0] = (r * sa) * cp;
+      o[1] = (r * sa) * sp;
+      o[2] = r * ca;
+    } else if (mode == RT_PRESET_LAT2D) {
+      o[0] = r * ca;
+      o[1] = r * sa;
+    } else {
+      o[0] = r * sa;
+      o[1] = r * ca;
+    }
+    o[nd - 1] = (k + 1 < cnt) ? src[(size_t)(k + 1) * ncol] - t : 0.0;
+  }
+}
+
+extern "C" int rt_traj_derived_columns(rt_ctx *ctx) {
+  if (!ctx) return set_err(ctx, RT_ERR_INVALID, "rt_traj_derived_columns: null context");
+  return ctx->env.preset == RT_PRESET_RAY3D ? 4 : 3;
+}
+
+extern "C" int rt_traj_derived(rt_ctx *ctx, const int64_t *offsets, double *out) {
+  if (!ctx || !offsets || !out) return set_err(ctx, RT_ERR_INVALID, "rt_traj_derived: null argument");
+  if (ctx->last_mode < 0 || ctx->last_max_samples <= 0)
+    return set_err(ctx, RT_ERR_STATE, "rt_traj_derived: the last solve did not save trajectories (save_mode = 0)");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  const long long n = ctx->last_n;
+  const int ncol = ctx->last_mode == RT_PRESET_RAY3D ? 8 : 9, nd = ctx->last_mode == RT_PRESET_RAY3D ? 4 : 3;
+  const int64_t total = offsets[n];
+  if (total == 0) return RT_OK;
+  long long *d_off = nullptr;
+  double *d_out = nullptr;
+  RT_CUDA(ctx, cudaMalloc(&d_off, (size_t)(n + 1) * sizeof(long long)));
+  cudaError_t e = cudaMalloc(&d_out, (size_t)total * nd * sizeof(double));
+  if (e != cudaSuccess) {
+    cudaFree(d_off);
+    return set_err(ctx, RT_ERR_NOMEM, "rt_traj_derived: %s", cudaGetErrorString(e));
+  }
+  cudaMemcpyAsync(d_off, offsets, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream);
+  rt_traj_derived_kernel<<<(unsigned)n, 64, 0, ctx->stream>>>(n, ctx->last_max_samples, ncol, ctx->last_mode, ctx->traj,
+                                                             d_off, d_out);
+  cudaMemcpyAsync(out, d_out, (size_t)total * nd * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+  e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d_off);
+  cudaFree(d_out);
+  if (e != cudaSuccess) return set_err(ctx, RT_ERR_CUDA, "rt_traj_derived: %s", cudaGetErrorString(e));
+  return RT_OK;
+}
+
 // census of exact-path fallbacks since the last reset (diagnostics)
 extern "C" int rt_debug_fallback_counts(rt_ctx *ctx, unsigned long long *out8, int reset) {
   if (!ctx || !out8) return set_err(ctx, RT_ERR_INVALID, "rt_debug_fallback_counts: null argument");

@@ -66,3 +66,20 @@ def launch_angle(b, hbi=1.0e6, re=RE):
     alpha = _np.arccos((re * _np.sin(b) ** 2.0 + _np.cos(b) * ((re + hbi) ** 2.0 - re ** 2.0 * _np.sin(b) ** 2.0) ** 0.5)
                        / (re + hbi))
     return alpha, b - alpha
+
+
+def index_surface(x=9.031e6, y=1.537e6, psi=None):
+    """The refractive-index-surface sweep of RayTrace_lat.jl:380-392: at the point (x, y) of the meridian plane,
+    lambda = atan|y/x|, r = sqrt(x^2 + y^2), dip = atan(2 tan lambda), and for every wave-normal angle psi
+    (default 0:0.001:2pi) the chi that produces it, chi = -psi + 3pi/2 - dip.  Returns (r, lambda, chi[], psi[]);
+    feed them to RayTracer.phase_refractive_index(r, lambda, chi, f) — one batch call on the GPU instead of the
+    reference's broadcast — for mu(psi) and dmu/dpsi(psi)."""
+    import numpy as _np
+    if psi is None:
+        psi = _np.arange(0.0, 2.0 * _np.pi, 0.001)
+    psi = _np.asarray(psi, dtype=_np.float64)
+    lam = _np.arctan(abs(y / x))
+    r = _np.sqrt(x ** 2 + y ** 2)
+    dip = _np.arctan(2.0 * _np.tan(lam))
+    chi = -1.0 * psi + 3.0 * _np.pi / 2 - dip
+    return float(r), float(lam), chi, psi

@@ -210,6 +210,49 @@ def test_branch_free_rhs_vouches_only_for_exact_bits_on_wild_states():
     assert ok[:100].all() and nan_e[:100].all()  # NaN radius
 
 
+def test_trajectory_post_processing_on_the_device():
+    """x = r cos(lam), y = r sin(lam), dt series (RayTrace_lat.jl:351-352,369-372) from the saved
+    trajectories, against the oracle's sin / cos on the copied samples (bit-exact)."""
+    for preset, launch in (("lat2d", sweeps.sweep_2d(3, 4)), ("raymain", sweeps.sweep_2d(2, 3)), ("ray3d", sweeps.sweep_3d(2, 2, 3))):
+        rt = R.RayTracer(preset)
+        rt.set_solver(maxiters=300, save_mode=1, max_samples=256)
+        res = rt.solve(launch, derived=True)
+        rt.close()
+        tr, d = res.traj, res.traj_derived
+        assert d.shape == (tr.shape[0], 4 if preset == "ray3d" else 3) and tr.shape[0] > launch.shape[1] * 20
+        r, a = tr[:, 1], tr[:, 2]
+        sa, ca = O.math("sin", a), O.math("cos", a)
+        if preset == "ray3d":
+            sp, cp = O.math("sin", tr[:, 3]), O.math("cos", tr[:, 3])
+            want = [(r * sa) * cp, (r * sa) * sp, r * ca]
+        elif preset == "lat2d":
+            want = [r * ca, r * sa]
+        else:
+            want = [r * sa, r * ca]
+        for k, w in enumerate(want):
+            assert _same(d[:, k], w), (preset, k)
+        dt = np.zeros(tr.shape[0])
+        dt[:-1] = tr[1:, 0] - tr[:-1, 0]
+        dt[res.traj_offsets[1:] - 1] = 0.0  # the last sample of each ray
+        assert _same(d[:, -1], dt), preset
+        k = launch.shape[1] - 1
+        assert np.array_equal(res.derived(k), d[res.traj_offsets[k]:res.traj_offsets[k + 1]])
+
+
+def test_refractive_index_surface_sweep():
+    """RayTrace_lat.jl:380-399 as one batch call: mu(psi), dmu/dpsi(psi) at the reference's test point."""
+    r, lam, chi, psi = sweeps.index_surface()
+    assert psi.size == 6284 and abs(r - np.hypot(9.031e6, 1.537e6)) < 1e-6
+    rt = R.RayTracer("lat2d")
+    mu, dmu = rt.phase_refractive_index(r, lam, chi, 5000.0)
+    rt.close()
+    E = O.env(O.LAT2D)
+    for k in (0, 1571, 3142, 6283):
+        m, d = O.phase_refractive_index_2d(E, r, lam, chi[k], 5000.0)[:2]
+        assert _same(np.array([mu[k], dmu[k]]), np.array([m, d])), k
+    assert np.isfinite(mu).all() and mu.min() > 1.0
+
+
 def test_two_chains_and_one_chain_give_identical_results():
     """Rays that start upward go to the priority chain (scheduling only)."""
     launch = sweeps.sweep_3d(12, 3, 24)
