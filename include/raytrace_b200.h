@@ -57,7 +57,8 @@ typedef enum rt_status {
  * plasmasphere pre-solve RayTrace_lat.jl:21-41.  Fill with rt_env_preset(). */
 typedef struct rt_env_params {
   int32_t preset;        /* rt_preset */
-  int32_t reserved;
+  int32_t density_model; /* 0 = the ray-tracing files' density: CA92(L) + exponential ionosphere (RayTrace_lat.jl:69-83);
+                            1 = plasmasphere.jl's composition (:171): diffusive_equilibrium(r, CA92(L)) + ionosphere_eq(r) */
   double c, re, B0, e, me, mp, eps; /* physical constants */
   double Lppi;           /* 5.6 - 0.46 Kp_max */
   double Lppo;           /* argmin |ne2 - ne3| over the L grid */
@@ -140,6 +141,10 @@ RT_API int rt_haselgrove_3d(rt_ctx *ctx, int64_t n, const double *u, const doubl
  * out5 is [5][n]: L, plasmasphere_eq, diffusive_equilibrium, ionosphere_eq, ne_total (cm^-3).  Lppi, Lppo, ne_Lppi,
  * the seasonal bracket and mlt come from the environment (2D presets only). */
 RT_API int rt_plasmasphere_density(rt_ctx *ctx, int64_t n, const double *r, const double *lam, double *out5);
+/* meridian-plane maps on the grid x[nx] x y[ny] (metres), plasmasphere.jl:157-175 and RayTrace_3D.jl:504-517:
+ * out4 = [L_xy, ne_total (diffusive_equilibrium(r, plasmasphere_eq(L)) + ionosphere_eq(r), cm^-3), log10 ne_total,
+ * |B| (B0 (re/r)^3 (1 + 3 cos^2(theta)), as the file writes it)][nx*ny], index ix*ny + iy */
+RT_API int rt_meridian_maps(rt_ctx *ctx, int64_t nx, int64_t ny, const double *x, const double *y, double *out4);
 
 /* ---- the solve: ODEProblem + solve over a launch list --------------------------------------- */
 /* 2D launch list columns (r, theta, chi, f, t) as in README.md:11; RayTrace_lat.jl:333-338 */

@@ -6,7 +6,7 @@ module RayTraceB200
 const LIB = get(ENV, "RAYTRACE_B200_LIB", joinpath(@__DIR__, "..", "ray-trace_b200", "libraytrace_b200.so"))
 
 struct EnvParams      # rt_env_params
-    preset::Int32; reserved::Int32
+    preset::Int32; density_model::Int32
     c::Float64; re::Float64; B0::Float64; e::Float64; me::Float64; mp::Float64; eps::Float64
     Lppi::Float64; Lppo::Float64; ne_Lppi::Float64; ca_coef::Float64; ca_trough::Float64
     iono_n0::Float64; iono_k::Float64; iono_h::Float64

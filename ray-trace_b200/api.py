@@ -30,7 +30,7 @@ STATUS_NAMES = {1: "Success", 2: "Terminated", 3: "Escaped", 4: "MaxIters", 5: "
 class EnvParams(C.Structure):
     """rt_env_params (include/raytrace_b200.h)."""
 
-    _fields_ = [("preset", C.c_int32), ("reserved", C.c_int32)] + [
+    _fields_ = [("preset", C.c_int32), ("density_model", C.c_int32)] + [
         (k, C.c_double)
         for k in ("c", "re", "B0", "e", "me", "mp", "eps", "Lppi", "Lppo", "ne_Lppi", "ca_coef", "ca_trough", "iono_n0",
                   "iono_k", "iono_h")
@@ -246,6 +246,15 @@ class RayTracer:
         out = np.zeros((5, n))
         _check(_lib().rt_plasmasphere_density(self._ctx, C.c_int64(n), _ptr(r), _ptr(lam), _ptr(out)), self._ctx)
         return dict(zip(("L", "plasmasphere_eq", "diffusive_equilibrium", "ionosphere_eq", "ne_total"), out))
+
+    def meridian_maps(self, x, y):
+        """plasmasphere.jl:157-175 / RayTrace_3D.jl:504-517 on the grid x[nx] × y[ny] (metres): dict of [nx, ny]
+        arrays L, ne_total (cm^-3), log10_ne_total, Bmag — the inputs of the reference's heatmaps and L contours."""
+        x = np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+        y = np.ascontiguousarray(np.asarray(y, dtype=np.float64))
+        out = np.zeros((4, x.size * y.size))
+        _check(_lib().rt_meridian_maps(self._ctx, C.c_int64(x.size), C.c_int64(y.size), _ptr(x), _ptr(y), _ptr(out)), self._ctx)
+        return {k: out[i].reshape(x.size, y.size) for i, k in enumerate(("L", "ne_total", "log10_ne_total", "Bmag"))}
 
     def debug_rhs3d(self, u, freq):
         """Diagnostics: both versions of the 3D right-hand side on chosen states u [n, 7] at frequency freq [n]:

@@ -194,6 +194,7 @@ static void make_dev_env(const rt_env_params &e, RtDevEnv &d) {
   d.iono_k = e.iono_k;
   d.iono_h = e.iono_h;
   d.inv_c = 1.0 / e.c;
+  d.density_model = e.density_model;
 }
 
 static int refresh_rcp(rt_ctx *ctx) {
@@ -321,6 +322,8 @@ extern "C" void rt_destroy(rt_ctx *ctx) {
 extern "C" int rt_set_env(rt_ctx *ctx, const rt_env_params *env) {
   if (!ctx || !env) return set_err(ctx, RT_ERR_INVALID, "rt_set_env: null argument");
   if (env->preset < 0 || env->preset > 3) return set_err(ctx, RT_ERR_INVALID, "rt_set_env: bad preset %d", env->preset);
+  if (env->density_model < 0 || env->density_model > 1)
+    return set_err(ctx, RT_ERR_INVALID, "rt_set_env: bad density_model %d", env->density_model);
   ctx->env = *env;
   make_dev_env(ctx->env, ctx->denv);
   return refresh_rcp(ctx);
@@ -517,6 +520,61 @@ extern "C" int rt_plasmasphere_density(rt_ctx *ctx, int64_t n, const double *r, 
   rt_plasmasphere_kernel<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->denv, n, d, d + n, d + 2 * n);
   RT_CUDA(ctx, cudaGetLastError());
   RT_CUDA(ctx, cudaMemcpyAsync(out5, d + 2 * n, 5 * nb, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
+// Meridian-plane maps: plasmasphere.jl:157-175 on a grid x[nx] x y[ny] in metres — r_xy :160,
+// theta_xy :161, L_xy :164, ne_total = diffusive_equilibrium(r, plasmasphere_eq(L)) + ionosphere_eq(r) :171,
+// log10 :174 — and the |B| map of RayTrace_3D.jl:514 (B0 (1/r)^3 (1 + 3 cos cos) as written, r in Earth radii).
+// out = [L, ne_total, log10 ne_total, Bmag][nx*ny], index ix*ny + iy.
+__global__ void rt_meridian_maps_kernel(const __grid_constant__ RtDevEnv E, long long nx, long long ny, const double *x,
+                                        const double *y, double *out) {
+  const long long n = nx * ny;
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const double xx = x[k / ny], yy = y[k % ny];
+  const double r = RT_SQRT(xx * xx + yy * yy);
+  const double th = rt_atan(yy / xx);
+  const double c = rt_cos(th);
+  const double L = (r / E.re) / (c * c);
+  double ne_eq = 0.0;
+  if (L <= E.Lppi) {
+    ne_eq = rt_exp10((-0.3145 * L + 3.9043) + E.ca_coef * rt_exp((2.0 - L) / 1.5));
+  } else if (E.Lppi < L && L <= E.Lppo) {
+    ne_eq = E.ne_Lppi * rt_exp10((E.Lppi - L) / 0.1);
+  } else if (E.Lppo < L) {
+    ne_eq = E.ca_trough * rt_pow_m4p5(L) + (1.0 - rt_exp((2.0 - L) / 10.0));
+  }
+  const double T = 2500.0, rb = 7370000.0;
+  const double G = rb * (1.0 - rb / r);
+  const double qb = rb / 7370.0;
+  const double S = ((1.506 * T) * (qb * qb)) * (1.0 / 1.0);
+  const double ne = ne_eq * RT_SQRT(1.0 * rt_exp(-G / S)) + 1e5 * rt_exp(-10.0 * ((r / E.re) - 1.0471));
+  const double q = 1.0 / (r / E.re);
+  out[k] = L;
+  out[n + k] = ne;
+  out[2 * n + k] = rt_log10(ne);
+  out[3 * n + k] = (E.B0 * ((q * q) * q)) * (1.0 + (3.0 * c) * c);
+}
+
+extern "C" int rt_meridian_maps(rt_ctx *ctx, int64_t nx, int64_t ny, const double *x, const double *y, double *out4) {
+  if (!ctx || nx < 0 || ny < 0 || (nx * ny > 0 && (!x || !y || !out4)))
+    return set_err(ctx, RT_ERR_INVALID, "rt_meridian_maps: bad argument");
+  if (ctx->env.preset == RT_PRESET_RAY3D)
+    return set_err(ctx, RT_ERR_INVALID,
+                   "rt_meridian_maps: plasmasphere.jl uses the RayTrace_lat.jl seasonal term; the environment preset is "
+                   "RT_PRESET_RAY3D");
+  const int64_t n = nx * ny;
+  if (n == 0) return RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (int rc = ensure_stage(ctx, (size_t)(nx + ny + 4 * n) * sizeof(double), 0)) return rc;
+  double *d = ctx->stage_d;
+  RT_CUDA(ctx, cudaMemcpyAsync(d, x, (size_t)nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  RT_CUDA(ctx, cudaMemcpyAsync(d + nx, y, (size_t)ny * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  rt_meridian_maps_kernel<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->denv, nx, ny, d, d + nx, d + nx + ny);
+  RT_CUDA(ctx, cudaGetLastError());
+  RT_CUDA(ctx, cudaMemcpyAsync(out4, d + nx + ny, (size_t)4 * n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return RT_OK;
 }

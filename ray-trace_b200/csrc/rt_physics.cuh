@@ -32,6 +32,7 @@ struct RtDevEnv {
   // device by rt_env_rcp_kernel with the division's own Newton sequence, and 1/c (an IEEE quotient, host-computed)
   double y_re, y_eps_me, y_eps_mp, y_me, y_mp, y_1p5, y_10, y_0p1, y_dth, y_df;
   double inv_c;
+  int density_model;  // rt_env_params.density_model
 };
 
 struct RtPlasma {  // local medium at one point (independent of wave frequency)
@@ -59,6 +60,15 @@ __device__ __forceinline__ double rt_density_cm3(const RtDevEnv &E, double r, do
   if (seg1) ne_plasma = p10;
   if (seg2) ne_plasma = E.ne_Lppi * p10;
   if (seg3) ne_plasma = E.ca_trough * rt_pow_m4p5(Lshell) + (1.0 - ex);
+  if (E.density_model == 1) {
+    // plasmasphere.jl's composition (:171): diffusive_equilibrium(r, CA92(L)) + ionosphere_eq(r), :96-117
+    const double T = 2500.0, rb = 7370000.0;
+    const double G = rb * (1.0 - rb / r);                       // :101
+    const double q = rb / 7370.0;
+    const double S = ((1.506 * T) * (q * q)) * (1.0 / 1.0);     // :102 (i = 1)
+    const double ne_de = ne_plasma * RT_SQRT(1.0 * rt_exp(-G / S));  // :105
+    return ne_de + 1e5 * rt_exp(-10.0 * ((r / E.re) - 1.0471));  // :115
+  }
   return ne_iono + ne_plasma;
 }
 

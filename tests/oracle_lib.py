@@ -16,7 +16,7 @@ LAT2D, RAY3D, RAYMAIN, SCRATCH = 0, 1, 2, 3
 
 
 class OrcEnv(C.Structure):
-    _fields_ = [("preset", C.c_int)] + [
+    _fields_ = [("preset", C.c_int), ("density_model", C.c_int)] + [
         (k, C.c_double)
         for k in ("c", "re", "B0", "e", "me", "mp", "eps", "Kp_max", "Lppi", "d", "Rbar", "mlt", "Lppo", "ne_Lppi")
     ]
@@ -183,6 +183,16 @@ def solve_test_ode(which, o, u0, t0=0.0, re_evt=0.0, cap=0):
 
 
 MATH = {"exp": 0, "exp10": 1, "log": 2, "log10": 3, "sin": 4, "cos": 5, "tan": 6, "atan": 7, "acos": 8, "pow_m4p5": 9}
+
+
+def meridian_maps(E, x, y):
+    """plasmasphere.jl:157-175 / RayTrace_3D.jl:504-517 on the grid x[nx] x y[ny] (metres):
+    [L, ne_total, log10 ne_total, |B|][nx*ny]."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    out = np.zeros((4, x.size * y.size))
+    lib().orc_meridian_maps(C.byref(E), C.c_int64(x.size), C.c_int64(y.size), _p(x), _p(y), _p(out))
+    return out
 
 
 def math(name, x):

@@ -253,6 +253,62 @@ def test_refractive_index_surface_sweep():
     assert np.isfinite(mu).all() and mu.min() > 1.0
 
 
+def test_plasmasphere_jl_composition_as_the_density_inside_mu():
+    """density_model = 1 puts diffusive_equilibrium(r, CA92(L)) + ionosphere_eq(r)
+    (plasmasphere.jl:96-117,171) under the refractive index; the integrate kernel then runs the exact code."""
+    r, lam, chi, f = _points_2d(1500, 21)
+    env = R.env_preset("lat2d")
+    env.density_model = 1
+    rt = R.RayTracer("lat2d", env=env)
+    E = O.env(O.LAT2D)
+    mu0 = np.array([O.phase_refractive_index_2d(E, *p)[0] for p in zip(r[:50], lam[:50], chi[:50], f[:50])])
+    E.density_model = 1
+    mu, dmu = rt.phase_refractive_index(r, lam, chi, f)
+    ref = np.array([O.phase_refractive_index_2d(E, *p) for p in zip(r, lam, chi, f)])
+    assert _same(mu, ref[:, 0]) and _same(dmu, ref[:, 1]) and not _same(mu[:50], mu0)
+    launch = sweeps.sweep_2d(3, 4)
+    rt.set_solver(maxiters=400)
+    res = rt.solve(launch)
+    rt.close()
+    _check_solve(res, O.solve_batch(E, O.opts(maxiters=400), launch, False, 4), 1e-10)
+
+    env3 = R.env_preset("ray3d")
+    env3.density_model = 1
+    rt = R.RayTracer("ray3d", env=env3)
+    E3 = O.env(O.RAY3D)
+    E3.density_model = 1
+    r, th, ph, rho, f = _points_3d(1000, 22)
+    u = np.vstack([r, th, ph, rho, np.zeros_like(r)])
+    du = rt.haselgrove(u, [f])
+    assert _same(du, np.array([O.haselgrove_3d(E3, u[:, k], f[k]) for k in range(r.size)]).T)
+    launch = sweeps.sweep_3d(3, 2, 4)
+    for coop in (-1, 10 ** 9):
+        rt.set_solver(maxiters=300, r_esc=10 * RE, coop_threshold=coop)
+        res = rt.solve(launch)
+        _check_solve(res, O.solve_batch(E3, O.opts(reltol=1e-3, dtmax=0, dtmin=0, maxiters=300, r_esc=10 * RE), launch, True, 4), 1e-7)
+    rt.close()
+    bad = R.env_preset("lat2d")
+    bad.density_model = 7
+    with pytest.raises(RuntimeError, match="density_model"):
+        R.RayTracer("lat2d", env=bad)
+
+
+def test_meridian_maps_bitexact():
+    """plasmasphere.jl:157-175 and RayTrace_3D.jl:504-517 as one batch kernel, against the oracle's loop."""
+    x = np.linspace(-4 * RE, 4 * RE, 81)  # includes x = 0 (y/x = +-Inf) and the origin (0/0)
+    y = np.linspace(-4 * RE, 4 * RE, 61)
+    rt = R.RayTracer("lat2d")
+    m = rt.meridian_maps(x, y)
+    rt.close()
+    ref = O.meridian_maps(O.env(O.LAT2D), x, y)
+    for i, k in enumerate(("L", "ne_total", "log10_ne_total", "Bmag")):
+        assert m[k].shape == (81, 61) and _same(m[k].ravel(), ref[i]), k
+    ix, iy = 60, 30  # x = 2 re, y = 0: L = 2, |B| = B0 / 8 * 4
+    assert abs(m["L"][ix, iy] - 2.0) < 1e-12 and abs(m["Bmag"][ix, iy] - O.env(O.LAT2D).B0 / 2.0) < 1e-18
+    with pytest.raises(RuntimeError, match="RAY3D"):
+        R.RayTracer("ray3d").meridian_maps(x, y)
+
+
 def test_two_chains_and_one_chain_give_identical_results():
     """Rays that start upward go to the priority chain (scheduling only)."""
     launch = sweeps.sweep_3d(12, 3, 24)

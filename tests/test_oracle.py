@@ -140,6 +140,26 @@ def test_plasmasphere_jl_functions():
     assert L.orc_diffusive_equilibrium(O._d(2 * 7370000.0), O._d(100.0)) < 100.0
 
 
+def test_composition_density_model_and_meridian_maps():
+    """density_model = 1 (plasmasphere.jl:171) changes mu through the density only; the maps of
+    plasmasphere.jl:157-175 agree with the scalar functions they are built from."""
+    E0, E1 = O.env(O.LAT2D), O.env(O.LAT2D)
+    E1.density_model = 1
+    r, lam, chi, f = 2.5 * RE, 0.4, 0.2, 4000.0
+    m0, m1 = O.phase_refractive_index_2d(E0, r, lam, chi, f), O.phase_refractive_index_2d(E1, r, lam, chi, f)
+    assert m0[0] != m1[0] and 0.3 < m1[0] / m0[0] < 1.0  # diffusive equilibrium thins the plasma: smaller mu
+    x, y = np.array([2 * RE, 3 * RE]), np.array([0.0, RE])
+    M = O.meridian_maps(E0, x, y)
+    assert M.shape == (4, 4) and M[0, 0] == 2.0 and M[3, 0] == E0.B0 / 2.0  # (2 re, 0): L = 2, B0 (1/2)^3 (1 + 3)
+    L = O.lib()
+    k = 3  # (3 re, re)
+    rr, th = math.hypot(3 * RE, RE), math.atan(1.0 / 3.0)
+    assert rel(M[0, k], (rr / RE) / math.cos(th) ** 2) < 1e-14
+    ne_eq = L.orc_plasmasphere_eq(O._d(M[0, k]), O._d(E0.Lppi), O._d(E0.Lppo), O._d(E0.d), O._d(E0.Rbar), O._d(E0.mlt))
+    want = L.orc_diffusive_equilibrium(O._d(rr), O._d(ne_eq)) + L.orc_ionosphere_eq(O._d(rr), O._d(RE))
+    assert rel(M[1, k], want) < 1e-13 and rel(M[2, k], math.log10(want)) < 1e-13
+
+
 def test_variant_presets_differ_as_the_files_do():
     r, th, chi, f = RE + 1e6, math.pi / 3, 0.3, 5000.0
     m_main = O.phase_refractive_index_2d(O.env(O.RAYMAIN), r, th, chi, f)
