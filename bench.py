@@ -308,6 +308,9 @@ def main():
         torch.cuda.synchronize()
         e2e_ms += 1e3 * (time.perf_counter() - t0)
     barrier()
+    # the host-pointer path (early result copy + late patch) must deliver what the device-resident path delivered
+    if int(res_h.nfe.astype(np.int64).sum()) != nfe_local or not np.array_equal(res_h.status, status_h):
+        raise RuntimeError("e2e results differ from the device-resident solve")
     h2d = ncol * n * 8
     d2h = (dim + 2) * n * 8 + 5 * n * 4
 

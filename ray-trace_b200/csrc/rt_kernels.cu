@@ -18,6 +18,8 @@
 
 static thread_local std::string g_last_error;
 
+#define RT_LATE_CAP 65536  // rays that may still be running when the early result copy starts
+
 struct rt_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;      // stream in use
@@ -36,6 +38,15 @@ struct rt_ctx {
   cudaStream_t aux_stream[2] = {nullptr, nullptr};  // second halves of the normal / priority list (chains 2 / 3)
   cudaEvent_t ev_chain[4] = {nullptr, nullptr, nullptr, nullptr}, ev_fork = nullptr;
   cudaEvent_t ev_join[3] = {nullptr, nullptr, nullptr};
+  // early result copy of the host-pointer entry points (see run_solve): results of the rays already finished go to
+  // the caller's pinned arrays while the long rays are still running; those are patched at the end
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_snap[4] = {nullptr, nullptr, nullptr, nullptr}, ev_copy = nullptr;
+  int *late_idx = nullptr, *late_i = nullptr, *late_hi = nullptr;  // device list, device / pinned packed int records
+  double *late_d = nullptr, *late_hd = nullptr;                    // device / pinned packed double records
+  const rt_result *early_host = nullptr;                           // non-null during a host-pointer solve with pinned results
+  bool early_done = false;
+  long long late_n = 0;
   double *traj = nullptr;
   size_t traj_bytes = 0;
   int *h_count = nullptr;  // pinned
@@ -264,6 +275,14 @@ extern "C" int rt_create(rt_ctx **out, int device) {
     for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_chain[k], cudaEventDisableTiming));
     RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     for (int k = 0; k < 3; k++) RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming));
+    RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_snap[k], cudaEventDisableTiming));
+    RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
+    RT_CUDA(ctx, cudaMalloc(&ctx->late_idx, RT_LATE_CAP * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->late_i, RT_LATE_CAP * 5 * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->late_d, RT_LATE_CAP * 9 * sizeof(double)));
+    RT_CUDA(ctx, cudaMallocHost(&ctx->late_hi, RT_LATE_CAP * 5 * sizeof(int)));
+    RT_CUDA(ctx, cudaMallocHost(&ctx->late_hd, RT_LATE_CAP * 9 * sizeof(double)));
   }
   rt_env_preset(RT_PRESET_LAT2D, &ctx->env);
   rt_solver_preset(RT_PRESET_LAT2D, &ctx->opts);
@@ -315,6 +334,15 @@ extern "C" void rt_destroy(rt_ctx *ctx) {
   if (ctx->prio_stream) cudaStreamDestroy(ctx->prio_stream);
   for (int k = 0; k < 2; k++)
     if (ctx->aux_stream[k]) cudaStreamDestroy(ctx->aux_stream[k]);
+  for (int k = 0; k < 4; k++)
+    if (ctx->ev_snap[k]) cudaEventDestroy(ctx->ev_snap[k]);
+  if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  cudaFree(ctx->late_idx);
+  cudaFree(ctx->late_i);
+  cudaFree(ctx->late_d);
+  cudaFreeHost(ctx->late_hi);
+  cudaFreeHost(ctx->late_hd);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -652,6 +680,21 @@ __global__ void rt_group_delay_kernel(long long n, const double *u_last, const d
   gd[i] = is3d ? u_last[i] : (u_last[i] - par[i]);  // RayTrace_3D.jl:356 / RayTrace_lat.jl:257,273
 }
 
+// terminal records of the rays listed in late_idx, packed component-major: od[(dim + 2)][m], oi[5][m]
+__global__ void rt_late_gather_kernel(int m, int dim, long long n, const int *late_idx, rt_result R, double *od, int *oi) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  const long long i = late_idx[j];
+  for (int c = 0; c < dim; c++) od[(size_t)c * m + j] = R.u_end[(size_t)c * n + i];
+  od[(size_t)dim * m + j] = R.t_end[i];
+  od[(size_t)(dim + 1) * m + j] = R.group_delay[i];
+  oi[j] = R.status[i];
+  oi[(size_t)m + j] = R.naccept[i];
+  oi[(size_t)2 * m + j] = R.nreject[i];
+  oi[(size_t)3 * m + j] = R.nfe[i];
+  oi[(size_t)4 * m + j] = R.nreflect[i];
+}
+
 template <int MODE>
 static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_result &R) {
   constexpr int DIM = RtTraits<MODE>::DIM, NCOL = RtTraits<MODE>::NCOL;
@@ -748,6 +791,20 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
     if (ch[c].upper > 0) RT_CUDA(ctx, cudaStreamWaitEvent(ch[c].st, ctx->ev_fork, 0));
   const bool dbg = getenv("RT_DEBUG") != nullptr;
   const int order[4] = {1, 3, 0, 2};  // priority chains first
+  // Early result copy (host-pointer entry points with pinned result arrays, large lists): once few rays are left,
+  // each chain — at its next batch boundary — saves its live list and records an event; after the four events the
+  // copy stream sends every result array to the caller while the long rays go on; their records are gathered and
+  // patched in after the end (solve_common).  Rays finished before a chain's event are final in memory by then.
+  const long long early_min = getenv("RT_EARLY_MIN") ? atoll(getenv("RT_EARLY_MIN")) : 262144;
+  const bool early = ctx->early_host != nullptr && n >= early_min;
+  // (late rays are patched in by a host scatter of 14 cache lines each, 0.13 us per ray: the snapshot waits until
+  // n / 512 rays are left — 2 ms before the end of cfg3, enough for its 92 MB)
+  static const long long early_div = getenv("RT_EARLY_DIV") ? atoll(getenv("RT_EARLY_DIV")) : 512;
+  const long long early_thr = (n / early_div < 1024) ? 1024 : ((n / early_div > RT_LATE_CAP) ? RT_LATE_CAP : n / early_div);
+  bool early_trigger = false, snap[4] = {false, false, false, false};
+  int nsnap = 0;
+  ctx->early_done = false;
+  ctx->late_n = 0;
   for (;;) {
     int npending = 0, nactive = 0, last_pending = -1;
     for (int oi = 0; oi < 4; oi++) {
@@ -770,6 +827,37 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
           }
         } else if (q != cudaErrorNotReady) {
           return set_err(ctx, RT_ERR_CUDA, "integrate chain %d: %s", c, cudaGetErrorString(q));
+        }
+      }
+      if (early && !ctx->early_done && !C.pending) {
+        if (!early_trigger && ch[0].upper + ch[1].upper + ch[2].upper + ch[3].upper <= early_thr) early_trigger = true;
+        if (early_trigger && !snap[c]) {
+          if (C.upper > 0)
+            RT_CUDA(ctx, cudaMemcpyAsync(ctx->late_idx + ctx->late_n, C.idx[C.cur], (size_t)C.upper * sizeof(int),
+                                         cudaMemcpyDeviceToDevice, C.st));
+          ctx->late_n += C.upper;
+          RT_CUDA(ctx, cudaEventRecord(ctx->ev_snap[c], C.st));
+          snap[c] = true;
+          if (++nsnap == 4) {
+            cudaStream_t cs = ctx->copy_stream;
+            const rt_result &H = *ctx->early_host;
+            const size_t nb = (size_t)n * sizeof(double), ib = (size_t)n * sizeof(int);
+            for (int q = 0; q < 4; q++) RT_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_snap[q], 0));
+            rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, cs>>>(n, R.u_end + (size_t)(DIM - 1) * n, ctx->par,
+                                                                    MODE == RT_PRESET_RAY3D, R.group_delay);
+            ctx->stats.kernel_launches++;
+            RT_CUDA(ctx, cudaMemcpyAsync(H.u_end, R.u_end, DIM * nb, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaMemcpyAsync(H.t_end, R.t_end, nb, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaMemcpyAsync(H.group_delay, R.group_delay, nb, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaMemcpyAsync(H.status, R.status, ib, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaMemcpyAsync(H.naccept, R.naccept, ib, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaMemcpyAsync(H.nreject, R.nreject, ib, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaMemcpyAsync(H.nfe, R.nfe, ib, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaMemcpyAsync(H.nreflect, R.nreflect, ib, cudaMemcpyDeviceToHost, cs));
+            RT_CUDA(ctx, cudaEventRecord(ctx->ev_copy, cs));
+            ctx->early_done = true;
+            if (dbg) fprintf(stderr, "[rt] early result copy enqueued, %lld rays still running\n", ctx->late_n);
+          }
         }
       }
       if (!C.pending && C.upper > 0) {
@@ -829,10 +917,19 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
       RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_join[c - 1], 0));
     }
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
+  if (ctx->early_done) RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_copy, 0));  // the early copy reads group_delay
   rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, R.u_end + (size_t)(DIM - 1) * n, ctx->par,
                                                           MODE == RT_PRESET_RAY3D, R.group_delay);
   RT_CUDA(ctx, cudaGetLastError());
   ctx->stats.kernel_launches++;
+  if (ctx->early_done && ctx->late_n > 0) {
+    const int m = (int)ctx->late_n;
+    rt_late_gather_kernel<<<grid_for(m, 128), 128, 0, st>>>(m, DIM, n, ctx->late_idx, R, ctx->late_d, ctx->late_i);
+    RT_CUDA(ctx, cudaGetLastError());
+    ctx->stats.kernel_launches++;
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->late_hd, ctx->late_d, (size_t)m * (DIM + 2) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->late_hi, ctx->late_i, (size_t)m * 5 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  }
   RT_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
   RT_CUDA(ctx, cudaStreamSynchronize(st));
   float ms_int = 0, ms_tot = 0;
@@ -898,8 +995,39 @@ static int solve_common(rt_ctx *ctx, int64_t n, const double *const *cols, int n
   D.nreject = D.naccept + n;
   D.nfe = D.nreject + n;
   D.nreflect = D.nfe + n;
-  if (int rc = dispatch_solve(ctx, n, L, D)) return rc;
+  // pinned result arrays allow the early asynchronous copy (pageable ones would block the scheduling loop)
+  const void *hp[8] = {res->u_end, res->t_end, res->group_delay, res->status, res->naccept, res->nreject, res->nfe, res->nreflect};
+  bool pinned = true;
+  for (int k = 0; k < 8 && pinned; k++) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, hp[k]) != cudaSuccess) {
+      cudaGetLastError();
+      pinned = false;
+    } else {
+      pinned = a.type == cudaMemoryTypeHost;
+    }
+  }
+  ctx->early_host = pinned ? res : nullptr;
+  const int rc_solve = dispatch_solve(ctx, n, L, D);
+  ctx->early_host = nullptr;
+  if (rc_solve) return rc_solve;
   cudaStream_t st = ctx->stream;
+  if (ctx->early_done) {
+    // everything but the rays that were still running at the snapshot is already in the caller's arrays
+    RT_CUDA(ctx, cudaEventSynchronize(ctx->ev_copy));
+    const size_t m = (size_t)ctx->late_n;
+    std::vector<int> li(m);
+    if (m) RT_CUDA(ctx, cudaMemcpy(li.data(), ctx->late_idx, m * sizeof(int), cudaMemcpyDeviceToHost));
+    int *ints[5] = {res->status, res->naccept, res->nreject, res->nfe, res->nreflect};
+    for (size_t j = 0; j < m; j++) {
+      const size_t i = (size_t)li[j];
+      for (int c = 0; c < dim; c++) res->u_end[(size_t)c * n + i] = ctx->late_hd[(size_t)c * m + j];
+      res->t_end[i] = ctx->late_hd[(size_t)dim * m + j];
+      res->group_delay[i] = ctx->late_hd[(size_t)(dim + 1) * m + j];
+      for (int q = 0; q < 5; q++) ints[q][i] = ctx->late_hi[(size_t)q * m + j];
+    }
+    return RT_OK;
+  }
   RT_CUDA(ctx, cudaMemcpyAsync(res->u_end, D.u_end, dim * nb, cudaMemcpyDeviceToHost, st));
   RT_CUDA(ctx, cudaMemcpyAsync(res->t_end, D.t_end, nb, cudaMemcpyDeviceToHost, st));
   RT_CUDA(ctx, cudaMemcpyAsync(res->group_delay, D.group_delay, nb, cudaMemcpyDeviceToHost, st));

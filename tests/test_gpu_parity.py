@@ -309,6 +309,35 @@ def test_meridian_maps_bitexact():
         R.RayTracer("ray3d").meridian_maps(x, y)
 
 
+def test_early_result_copy_into_pinned_arrays_matches_the_plain_copy(monkeypatch):
+    """rt_solve_3d with pinned result arrays sends the finished rays' records to the host while the long rays still
+    run and patches those in afterwards (run_solve / solve_common); RT_EARLY_MIN=0 enables it for a small list."""
+    import ctypes as C
+    import torch
+    launch = sweeps.sweep_3d(12, 3, 24)
+    n = launch.shape[1]
+    rt = R.RayTracer("ray3d")
+    rt.set_solver(maxiters=600, r_esc=10 * RE, coop_threshold=64)
+    plain = rt.solve(launch)  # pageable numpy arrays: one copy at the end
+    monkeypatch.setenv("RT_EARLY_MIN", "0")
+    res = R.api.SolveResult(n, 7)
+    keep = []
+    for name in ("u_end", "t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
+        t = torch.from_numpy(getattr(res, name)).pin_memory()
+        t.fill_(-7)
+        keep.append(t)
+        setattr(res, name, t.numpy())
+    cres = res._c()
+    lp = torch.from_numpy(np.ascontiguousarray(launch)).pin_memory()
+    cols = [C.c_void_p(lp[k].data_ptr()) for k in range(9)]
+    for _ in range(2):
+        assert R.api._lib().rt_solve_3d(rt._ctx, C.c_int64(n), *cols, C.byref(cres)) == 0
+        for k in ("u_end", "t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
+            assert _same(getattr(res, k), getattr(plain, k)), k
+    assert (plain.naccept + plain.nreject).max() == 600  # long rays were still running at the snapshot
+    rt.close()
+
+
 def test_two_chains_and_one_chain_give_identical_results():
     """Rays that start upward go to the priority chain (scheduling only)."""
     launch = sweeps.sweep_3d(12, 3, 24)
