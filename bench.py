@@ -34,11 +34,11 @@ RE = 6.3712e6
 # (profiles/r1_flop_calibration.md) and frozen.
 FLOP_PER_RHS = {"cfg3": 2602.0, "cfg2": 2307.0}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-list launch of rt_integrate_kernel (4 attempts for each of
-# 956 000 rays) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v2.md: 175.3 MB + 115.0 MB.
-# Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 956 000 = 0.38 GB-equivalent upper bound.
+# 10^6 rays, 7813 blocks) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v3.md:
+# 176.3 MB + 115.6 MB.  Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 10^6 = 0.4 GB upper bound.
 # launch-list partition across ranks: strided (rank, rank + N, ...) so that every GPU gets its share of the long rays
 PARTITION = "strided"
-NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 290.3e6, "cfg2": None}
+NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 291.9e6, "cfg2": 13.3e6}
 
 
 def parse():
@@ -352,7 +352,7 @@ def main():
                        "status_counts_rank0": {R.STATUS_NAMES[int(a)]: int(b) for a, b in zip(uniq, cnt)}},
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak / 1e12, "unit": "TFLOP/s",
                          "frac": achieved / (peak / 1e12), "traffic": NCU_DRAM_BYTES_PER_FULL_LAUNCH[args.workload],
-                         "traffic_note": "bytes per full-list launch (ncu, profiles/r1_ncu_integrate_v2.md); "
+                         "traffic_note": "bytes per full-list launch (ncu, profiles/r1_ncu_integrate_v3.md); "
                                          "0.09 TB/s: HBM is not the bound",
                          "steady_state": None if steady is None else dict(
                              steady, achieved=steady["rhs_evals_per_s"] * flop / 1e12,
