@@ -68,6 +68,11 @@ typedef struct rt_env_params {
   double iono_n0;        /* 1.8e5 cm^-3 */
   double iono_k;         /* -4.183119 */
   double iono_h;         /* 1.0471 */
+  /* [EXT] finite-difference steps of d(mu)/d(lam|theta) and d(mu)/dr (RayTrace_lat.jl:198-222, RayTrace_3D.jl:223-247).
+   * 0 = the files' 1.0e-11: the parity path, on which r -+ 5e-12 == r and d(mu)/dr is identically zero.  > 0 = a step
+   * FP64 can resolve (radians / metres, e.g. 1e-6 / 10): physically meaningful gradients, never bit-comparable with the
+   * reference; the integrate kernel then runs its exact right-hand side (7 refractive indices instead of 5) */
+  double fd_step_angle, fd_step_r;
 } rt_env_params;
 
 /* Solver options: the keyword arguments of solve(), RayTrace_lat.jl:338 / RayTrace_3D.jl:395. */

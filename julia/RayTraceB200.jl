@@ -10,6 +10,7 @@ struct EnvParams      # rt_env_params
     c::Float64; re::Float64; B0::Float64; e::Float64; me::Float64; mp::Float64; eps::Float64
     Lppi::Float64; Lppo::Float64; ne_Lppi::Float64; ca_coef::Float64; ca_trough::Float64
     iono_n0::Float64; iono_k::Float64; iono_h::Float64
+    fd_step_angle::Float64; fd_step_r::Float64   # 0 = the reference's 1e-11 (parity path)
 end
 
 mutable struct SolverOpts   # rt_solver_opts

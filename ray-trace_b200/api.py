@@ -33,7 +33,7 @@ class EnvParams(C.Structure):
     _fields_ = [("preset", C.c_int32), ("density_model", C.c_int32)] + [
         (k, C.c_double)
         for k in ("c", "re", "B0", "e", "me", "mp", "eps", "Lppi", "Lppo", "ne_Lppi", "ca_coef", "ca_trough", "iono_n0",
-                  "iono_k", "iono_h")
+                  "iono_k", "iono_h", "fd_step_angle", "fd_step_r")
     ]
 
 

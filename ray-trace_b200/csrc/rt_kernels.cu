@@ -206,6 +206,9 @@ static void make_dev_env(const rt_env_params &e, RtDevEnv &d) {
   d.iono_h = e.iono_h;
   d.inv_c = 1.0 / e.c;
   d.density_model = e.density_model;
+  d.h_ang = e.fd_step_angle > 0.0 ? e.fd_step_angle : 1.0e-11;
+  d.h_r = e.fd_step_r > 0.0 ? e.fd_step_r : 1.0e-11;
+  d.fd_default = !(e.fd_step_angle > 0.0) && !(e.fd_step_r > 0.0);
 }
 
 static int refresh_rcp(rt_ctx *ctx) {
@@ -352,6 +355,8 @@ extern "C" int rt_set_env(rt_ctx *ctx, const rt_env_params *env) {
   if (env->preset < 0 || env->preset > 3) return set_err(ctx, RT_ERR_INVALID, "rt_set_env: bad preset %d", env->preset);
   if (env->density_model < 0 || env->density_model > 1)
     return set_err(ctx, RT_ERR_INVALID, "rt_set_env: bad density_model %d", env->density_model);
+  if (!(env->fd_step_angle >= 0.0) || !(env->fd_step_r >= 0.0))
+    return set_err(ctx, RT_ERR_INVALID, "rt_set_env: finite-difference steps must be >= 0 (0 = the reference's 1e-11)");
   ctx->env = *env;
   make_dev_env(ctx->env, ctx->denv);
   return refresh_rcp(ctx);

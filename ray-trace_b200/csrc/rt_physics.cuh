@@ -33,6 +33,8 @@ struct RtDevEnv {
   double y_re, y_eps_me, y_eps_mp, y_me, y_mp, y_1p5, y_10, y_0p1, y_dth, y_df;
   double inv_c;
   int density_model;  // rt_env_params.density_model
+  int fd_default;     // 1: both finite-difference steps are the files' 1.0e-11 (the branch-free path's precondition)
+  double h_ang, h_r;  // finite-difference steps of d(mu)/d(theta|lambda), d(mu)/dr (rt_env_params.fd_step_*)
 };
 
 struct RtPlasma {  // local medium at one point (independent of wave frequency)
@@ -215,7 +217,7 @@ __device__ __forceinline__ void rt_haselgrove_2d(const RtDevEnv &E, const double
   for (int k = 0; k < 5; k++) {
     double f_k = freq;
     if (k < 3) {
-      double th_k = (k == 0) ? th : ((k == 1) ? th - 1.0e-11 / 2.0 : th + 1.0e-11 / 2.0);
+      double th_k = (k == 0) ? th : ((k == 1) ? th - E.h_ang / 2.0 : th + E.h_ang / 2.0);
       double d0, d1;
       rt_geo2d<PRESET>(E, r, th_k, chi, p, d0, d1);
       if (k == 0) {
@@ -234,14 +236,14 @@ __device__ __forceinline__ void rt_haselgrove_2d(const RtDevEnv &E, const double
     if (k == 3) m.mu_fl = v.mu;
     if (k == 4) m.mu_fr = v.mu;
   }
-  double dmudth = (m.mu_tr - m.mu_tl) / 1.0e-11;
+  double dmudth = (m.mu_tr - m.mu_tl) / E.h_ang;
   double dmudf = (m.mu_fr - m.mu_fl) / 1.0e-5;
-  double rl = r - 1.0e-11 / 2.0, rr = r + 1.0e-11 / 2.0;
+  double rl = r - E.h_r / 2.0, rr = r + E.h_r / 2.0;
   double dmudr;
   if (rl == r && rr == r) {
-    dmudr = (m.mu_c - m.mu_c) / 1.0e-11;  // 0.0, or NaN when mu is not finite
+    dmudr = (m.mu_c - m.mu_c) / E.h_r;  // 0.0, or NaN when mu is not finite
   } else {
-    dmudr = (rt_mu2d_slow<PRESET>(E, rr, th, chi, freq) - rt_mu2d_slow<PRESET>(E, rl, th, chi, freq)) / 1.0e-11;
+    dmudr = (rt_mu2d_slow<PRESET>(E, rr, th, chi, freq) - rt_mu2d_slow<PRESET>(E, rl, th, chi, freq)) / E.h_r;
   }
   double sc, cc;
   rt_sincos(chi, &sc, &cc);
@@ -317,7 +319,7 @@ __device__ __forceinline__ void rt_haselgrove_3d(const RtDevEnv &E, const double
   for (int k = 0; k < 5; k++) {
     double f_k = freq;
     if (k < 3) {
-      double th_k = (k == 0) ? th : ((k == 1) ? th - 1.0e-11 / 2.0 : th + 1.0e-11 / 2.0);
+      double th_k = (k == 0) ? th : ((k == 1) ? th - E.h_ang / 2.0 : th + E.h_ang / 2.0);
       rt_geo3d(E, r, th_k, rr_, rt_, rp_, g);
       if (k == 0) gc = g;
     } else {
@@ -334,15 +336,15 @@ __device__ __forceinline__ void rt_haselgrove_3d(const RtDevEnv &E, const double
   RtMu c;
   c.mu = m.mu_c;
   c.dmudpsi = m.dmudpsi;
-  double dmudt = (m.mu_tr - m.mu_tl) / 1.0e-11;
+  double dmudt = (m.mu_tr - m.mu_tl) / E.h_ang;
   double dmudf = (m.mu_fr - m.mu_fl) / 1.0e-5;
   double dmudp = (c.mu - c.mu) / 1.0e-11;  // mu independent of phi
-  double rl = r - 1.0e-11 / 2.0, rh = r + 1.0e-11 / 2.0;
+  double rl = r - E.h_r / 2.0, rh = r + E.h_r / 2.0;
   double dmudr;
   if (rl == r && rh == r) {
-    dmudr = (c.mu - c.mu) / 1.0e-11;
+    dmudr = (c.mu - c.mu) / E.h_r;
   } else {
-    dmudr = (rt_mu3d_slow(E, rh, th, rr_, rt_, rp_, freq) - rt_mu3d_slow(E, rl, th, rr_, rt_, rp_, freq)) / 1.0e-11;
+    dmudr = (rt_mu3d_slow(E, rh, th, rr_, rt_, rp_, freq) - rt_mu3d_slow(E, rl, th, rr_, rt_, rp_, freq)) / E.h_r;
   }
   double dmr = rt_ddrho(gc, c, rr_, 0);
   double dmt = rt_ddrho(gc, c, rt_, 1);

@@ -224,7 +224,7 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
   // 2^16 <= |r| < 2^513 (so that r -+ 5e-12 == r and d(mu)/dr is (mu - mu)/1e-11; trial stages overshoot to
   // negative radii routinely); rho_phi finite, non-zero
   ok = ok && ((unsigned)((__double2hiint(r) & 0x7fffffff) - 0x40f00000) < (0x60000000u - 0x40f00000u));
-  ok = ok && rtf_quarter_range(rp_) && (E.density_model == 0);  // other density models: exact code only
+  ok = ok && rtf_quarter_range(rp_) && (E.density_model == 0) && (E.fd_default != 0);  // other density models / steps: exact code only
   // Two inputs whose result is known without arithmetic — all seven derivatives NaN — and which the garbage trial
   // stages of a step about to be rejected hit often enough to matter (one lane on the exact path stalls its warp
   // for ~10 right-hand sides):
@@ -345,7 +345,7 @@ RTF void rtf_geo2d_lat(const RtDevEnv &E, const RtRad2D &R, double r, double th,
 template <bool COOP>
 RTF bool rtf_haselgrove_2d_lat(const RtDevEnv &E, const double *u, double *du, RtExtras2D *ex) {
   const double r = u[0], th = u[1], chi = u[2], freq = u[3];
-  bool ok = (E.density_model == 0);  // other density models: exact code only
+  bool ok = (E.density_model == 0) && (E.fd_default != 0);  // other density models / steps: exact code only
   ok = ok && ((unsigned)((__double2hiint(r) & 0x7fffffff) - 0x40f00000) < (0x60000000u - 0x40f00000u));
   const double two_pi = 2.0 * RT_PI;
   RtRad2D Rd;

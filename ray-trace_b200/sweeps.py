@@ -83,3 +83,16 @@ def index_surface(x=9.031e6, y=1.537e6, psi=None):
     dip = _np.arctan(2.0 * _np.tan(lam))
     chi = -1.0 * psi + 3.0 * _np.pi / 2 - dip
     return float(r), float(lam), chi, psi
+
+
+def normalize_rho(rt, launch):
+    """[EXT] a 3D launch list whose refractive-index vector has the length the medium gives it:
+    rho <- rho * mu(r, theta, phi, rho, f) / |rho| (mu depends on rho through its direction only).  The reference
+    launches with |rho| = 1 (RayTrace_3D.jl:390), which is not a solution of the dispersion relation; never used
+    on the parity path.  `rt` is a RayTracer("ray3d"); one batch call of refractive_index on the GPU."""
+    import numpy as _np
+    launch = _np.array(launch, dtype=_np.float64, copy=True)
+    mu = rt.refractive_index(launch[0], launch[1], launch[2], launch[3], launch[4], launch[5], launch[7])[0]
+    norm = _np.sqrt(launch[3] ** 2 + launch[4] ** 2 + launch[5] ** 2)
+    launch[3:6] *= mu / norm
+    return launch

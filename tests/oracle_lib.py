@@ -18,7 +18,8 @@ LAT2D, RAY3D, RAYMAIN, SCRATCH = 0, 1, 2, 3
 class OrcEnv(C.Structure):
     _fields_ = [("preset", C.c_int), ("density_model", C.c_int)] + [
         (k, C.c_double)
-        for k in ("c", "re", "B0", "e", "me", "mp", "eps", "Kp_max", "Lppi", "d", "Rbar", "mlt", "Lppo", "ne_Lppi")
+        for k in ("c", "re", "B0", "e", "me", "mp", "eps", "Kp_max", "Lppi", "d", "Rbar", "mlt", "Lppo", "ne_Lppi",
+                  "fd_step_angle", "fd_step_r")
     ]
 
 

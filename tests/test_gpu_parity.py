@@ -338,6 +338,38 @@ def test_early_result_copy_into_pinned_arrays_matches_the_plain_copy(monkeypatch
     rt.close()
 
 
+def test_resolvable_finite_difference_steps_are_an_option_off_the_parity_path():
+    """fd_step_angle / fd_step_r > 0 replace the files' 1e-11 (under which d(mu)/dr is identically 0
+    and d(mu)/d(theta) is rounding noise); oracle and kernels agree bit for bit with the option on as well."""
+    env = R.env_preset("ray3d")
+    env.fd_step_angle, env.fd_step_r = 1e-6, 10.0
+    E = O.env(O.RAY3D)
+    E.fd_step_angle, E.fd_step_r = 1e-6, 10.0
+    rt = R.RayTracer("ray3d", env=env)
+    r, th, ph, rho, f = _points_3d(600, 31)
+    u = np.vstack([r, th, ph, rho, np.zeros_like(r)])
+    du = rt.haselgrove(u, [f])
+    assert _same(du, np.array([O.haselgrove_3d(E, u[:, k], f[k]) for k in range(r.size)]).T)
+    du0 = R.RayTracer("ray3d").haselgrove(u, [f])
+    assert not _same(du[3], du0[3]) and _same(du[0], du0[0])  # d(rho_r)/dt now has its (1/mu) d(mu)/dr term
+    launch = sweeps.normalize_rho(rt, sweeps.sweep_3d(3, 2, 4))  # |rho| = mu at launch
+    mu = rt.refractive_index(*launch[:6], launch[7])[0]
+    assert np.allclose(np.sqrt((launch[3:6] ** 2).sum(axis=0)), mu, rtol=1e-14)
+    rt.set_solver(maxiters=300, r_esc=10 * RE)
+    res = rt.solve(launch)
+    _check_solve(res, O.solve_batch(E, O.opts(reltol=1e-3, dtmax=0, dtmin=0, maxiters=300, r_esc=10 * RE), launch, True, 4), 1e-7)
+    rt.close()
+    env2 = R.env_preset("lat2d")
+    env2.fd_step_angle, env2.fd_step_r = 1e-6, 10.0
+    E2 = O.env(O.LAT2D)
+    E2.fd_step_angle, E2.fd_step_r = 1e-6, 10.0
+    rt = R.RayTracer("lat2d", env=env2)
+    r, lam, chi, f = _points_2d(600, 32)
+    u = np.vstack([r, lam, chi, f])
+    assert _same(rt.haselgrove(u), np.array([O.haselgrove_2d(E2, u[:, k]) for k in range(u.shape[1])]).T)
+    rt.close()
+
+
 def test_two_chains_and_one_chain_give_identical_results():
     """Rays that start upward go to the priority chain (scheduling only)."""
     launch = sweeps.sweep_3d(12, 3, 24)
