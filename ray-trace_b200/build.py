@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("RT_LIB") or os.path.join(HERE, "libraytrace_b200.so")  # RT_LIB: developer override (variant builds)
 SOURCES = ["rt_kernels.cu", "rt_selftest.cu"]
-HEADERS = ["rt_math.h", "rt_fast.cuh", "rt_physics.cuh", "rt_integrate.cuh", os.path.join("..", "..", "include", "raytrace_b200.h")]
+HEADERS = ["rt_math.h", "rt_fast.cuh", "rt_physics.cuh", "rt_physics_fast.cuh", "rt_integrate.cuh", os.path.join("..", "..", "include", "raytrace_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-t", "0", "-lineinfo", "-std=c++17",
