@@ -36,8 +36,9 @@ FLOP_PER_RHS = {"cfg3": 2602.0, "cfg2": 2307.0}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-list launch of rt_integrate_kernel (4 attempts for each of
 # 10^6 rays, 7813 blocks) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v3.md:
 # 176.3 MB + 115.6 MB.  Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 10^6 = 0.4 GB upper bound.
-# launch-list partition across ranks: strided (rank, rank + N, ...) so that every GPU gets its share of the long rays
-PARTITION = "strided"
+# launch-list partition across ranks: block b of N consecutive rays goes to the ranks rotated by b, so that every GPU
+# gets its share of the long rays AND of every wave-normal angle (plain strided: +-4.5 % work per rank on 8 GPUs)
+PARTITION = "rotated"
 NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 291.9e6, "cfg2": 13.3e6}
 
 
@@ -322,8 +323,12 @@ def main():
         dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         ms_all, e2e_all = float(tmax[0]), float(tmax[1])
         nfe_all, rays_all, launches_all = float(tsum[0]), float(tsum[1]), float(tsum[2])
+        per_rank = [torch.zeros(2, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(per_rank, torch.tensor([ms_local, nfe_local], dtype=torch.float64, device=dev))
+        by_rank = [{"ms_per_step": float(t[0]) / args.steps, "rhs_evals_per_step": int(t[1])} for t in per_rank]
     else:
         ms_all, e2e_all, nfe_all, rays_all, launches_all = ms_local, e2e_ms, float(nfe_local), float(n), float(launches)
+        by_rank = None
 
     if rank == 0:
         K = args.steps
@@ -365,6 +370,7 @@ def main():
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_all / K,
                     "rays_per_s": rays_all * K / (e2e_all * 1e-3)},
             "gpu_launches": int(launches_all),
+            "by_rank": by_rank,
             "clocks": clocks,
         }
         print(json.dumps(line), flush=True)

@@ -47,12 +47,21 @@ def partition(n, rank, world):
 
 
 def partition_indices(n, rank, world, layout="contiguous"):
-    """Launch-list indices of rank `rank`: "contiguous" = [lo, hi) as partition(); "strided" = rank, rank + world, ...
+    """Launch-list indices of rank `rank`: "contiguous" = [lo, hi) as partition(); "strided" = rank, rank + world, ...;
+    "rotated" = strided with the rank order rotated from one block of `world` rays to the next.
     Rays are independent, so any partition gives the same per-ray results; strided balances sweeps whose expensive
     rays cluster in one part of the launch list (cfg3: the long magnetospheric paths sit at high colatitude)."""
     import numpy as _np
     if layout == "strided":
         return _np.arange(rank, n, world)
+    if layout == "rotated":
+        # block b of `world` consecutive rays goes to the ranks rotated by b: rank r takes offset (r - b) mod world.
+        # Like strided, but a rank no longer sees only the indices congruent to r modulo gcd(world, inner sweep
+        # length): with 100 wave-normal angles innermost and 8 ranks, strided hands each rank 25 of the 100 angles
+        # and the per-rank work differs by +-4.5 %.
+        b = _np.arange((n + world - 1) // world, dtype=_np.int64)
+        idx = b * world + (rank - b) % world
+        return idx[idx < n]
     lo, hi = partition(n, rank, world)
     return _np.arange(lo, hi)
 

@@ -48,7 +48,7 @@ def _worker(rank, world, port, out_path, n_total, layout):
 import pytest
 
 
-@pytest.mark.parametrize("layout", ["contiguous", "strided"])
+@pytest.mark.parametrize("layout", ["contiguous", "strided", "rotated"])
 def test_two_rank_partition_and_gather(tmp_path, layout):
     from raytrace_b200 import sweeps
     n_total = 101  # odd: ragged partitions 50 + 51
