@@ -370,6 +370,45 @@ def test_resolvable_finite_difference_steps_are_an_option_off_the_parity_path():
     rt.close()
 
 
+def test_edge_sizes_and_every_termination_class():
+    """Empty, single-ray and ragged launch lists (n % 128 != 0, n % 40 != 0), and every status the solver can
+    return — Success (t1 reached), Terminated (ground), Escaped, MaxIters, DtLessThanMin — against the oracle."""
+    rt3 = R.RayTracer("ray3d")
+    full = sweeps.sweep_3d(5, 3, 9)  # 135 rays
+    res = rt3.solve(full[:, :0])
+    assert res.status.size == 0 and res.u_end.shape == (7, 0)
+    E3 = O.env(O.RAY3D)
+    cases = [
+        dict(maxiters=40),                                   # MaxIters for every ray
+        dict(maxiters=400, r_esc=RE + 1.2e6),                # upward rays escape at once, the others reach the ground
+        dict(maxiters=400, dtmin=5e6, dtmax=1e9),            # DtLessThanMin after the first rejections
+        dict(maxiters=400, t1=2.0e-3),                       # Success: tspan ends first
+    ]
+    seen = set()
+    for kw in cases:
+        okw = dict(dict(reltol=1e-3, dtmax=0, dtmin=0, maxiters=400), **kw)
+        for n in (1, 129, 135):
+            for coop in (-1, 10 ** 9):
+                rt3.set_solver(**dict(dict(r_esc=0.0, dtmin=0.0, dtmax=0.0, t1=5.0e9), **kw, coop_threshold=coop))
+                res = rt3.solve(full[:, :n])
+                _check_solve(res, O.solve_batch(E3, O.opts(**okw), full[:, :n], True, 2), 1e-7)
+                seen |= set(int(v) for v in np.unique(res.status))
+    names = {R.STATUS_NAMES[v] for v in seen}
+    # (DtNaN: the sweep's chi = 0 column has rho_theta = 0, the reference's own 0/0, RayTrace_3D.jl:304-310)
+    assert {"Success", "Terminated", "Escaped", "MaxIters", "DtLessThanMin", "DtNaN"} <= names, names
+    with pytest.raises(ValueError, match="launch list"):
+        rt3.solve(sweeps.sweep_2d(2, 2))
+    rt3.close()
+    rt2 = R.RayTracer("lat2d")
+    launch = sweeps.sweep_2d(7, 19)  # 133 rays
+    for n in (1, 133):
+        for coop in (-1, 10 ** 9):
+            rt2.set_solver(maxiters=150, coop_threshold=coop)
+            res = rt2.solve(launch[:, :n])
+            _check_solve(res, O.solve_batch(O.env(O.LAT2D), O.opts(maxiters=150), launch[:, :n], False, 2), 1e-10)
+    rt2.close()
+
+
 def test_two_chains_and_one_chain_give_identical_results():
     """Rays that start upward go to the priority chain (scheduling only)."""
     launch = sweeps.sweep_3d(12, 3, 24)
