@@ -1,12 +1,15 @@
 #!/usr/bin/env python
 """bench.py — RHS evaluations/s and rays/s of the batched whistler ray tracer on N B200s.
 
-Workload (config.workload): "cfg3" = BASELINE.json configs[2], the 3D (RayTrace_3D.jl) sweep of 10^6 rays over
-colatitude x longitude x wave-normal angle that north_star's target is quoted on.  At N GPUs the sweep is refined
-along longitude to N*10^6 rays and partitioned across ranks (strided: rank, rank + N, ...) (weak scaling, no data-path collective); the one
-exchange is the gather of terminal records to rank 0 (inside the timed step for N > 1).
+Workload (config.workload): "cfg3" (default) = BASELINE.json configs[2], the 3D (RayTrace_3D.jl) sweep of 10^6 rays
+over colatitude x longitude x wave-normal angle that north_star's target is quoted on.  At N GPUs the sweep is refined
+along longitude to N*10^6 rays and partitioned across ranks (rotated-strided; weak scaling, no data-path collective);
+the one exchange is the gather of terminal records to rank 0 (inside the timed step for N > 1).
+Other workloads (records under profiles/, not the driver's line): "cfg2" = configs[1], 10^5-ray 2D sweep; "cfg4" =
+configs[3], 10^6 long-duration 2D rays (tspan 5e10, reltol 1e-7, maxiters 10^6: minutes per step, run it with
+--steps 1 --warmup 0); "cfg5" = configs[4], the FIXED 10^7-ray 3D list partitioned over the ranks (strong scaling).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3|cfg2] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3|cfg2|cfg4|cfg5] [--impl ours|reference]
 
 A step = one full solve of the rank's launch list (init kernel + integrate slices + group-delay kernel).
 value      : RHS evaluations/s, launch list and results resident in HBM (device-pointer C-ABI entry point)
@@ -32,14 +35,16 @@ RE = 6.3712e6
 # Algorithmic FP64 work per Haselgrove RHS evaluation: executed
 # DADD + DMUL + 2*DFMA per RHS of the minimal faithful schedule, calibrated once with ncu
 # (profiles/r1_flop_calibration.md) and frozen.
-FLOP_PER_RHS = {"cfg3": 2602.0, "cfg2": 2307.0}
+FLOP_PER_RHS = {"cfg3": 2602.0, "cfg5": 2602.0, "cfg2": 2307.0, "cfg4": 2307.0}
+IS3D = {"cfg3": True, "cfg5": True, "cfg2": False, "cfg4": False}
+SCALING = {"cfg3": "weak", "cfg2": "weak", "cfg4": "weak", "cfg5": "strong"}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-list launch of rt_integrate_kernel (4 attempts for each of
 # 10^6 rays, 7813 blocks) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v3.md:
 # 176.3 MB + 115.6 MB.  Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 10^6 = 0.4 GB upper bound.
 # launch-list partition across ranks: block b of N consecutive rays goes to the ranks rotated by b, so that every GPU
 # gets its share of the long rays AND of every wave-normal angle (plain strided: +-4.5 % work per rank on 8 GPUs)
 PARTITION = "rotated"
-NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 291.9e6, "cfg2": 13.3e6}
+NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 291.9e6, "cfg5": None, "cfg2": 13.3e6, "cfg4": None}
 
 
 def parse():
@@ -47,11 +52,12 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg2"])
+    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg2", "cfg4", "cfg5"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays-per-gpu", type=int, default=0, help="override (testing only)")
     ap.add_argument("--slice", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=0, help="rays in the CPU sample (0 = default)")
+    ap.add_argument("--maxiters", type=int, default=0, help="iteration cap override (a cut-off run: named in config)")
     return ap.parse_args()
 
 
@@ -64,6 +70,13 @@ def make_launch(workload, world, rank, rays_per_gpu=0):
             full = sweeps.sweep_3d(k, k * world, 100)
         else:
             full = sweeps.sweep_3d(100, 100 * world, 100)
+    elif workload == "cfg5":  # the fixed 10^7-ray list (cfg3's grid refined along longitude), whatever the world size
+        full = sweeps.sweep_3d(100, max(1, rays_per_gpu // 10000) if rays_per_gpu else 1000, 100)
+    elif workload == "cfg4":
+        if rays_per_gpu:
+            full = sweeps.sweep_2d_long(max(1, rays_per_gpu // 1000) * world, 1000)
+        else:
+            full = sweeps.sweep_2d_long(1000 * world, 1000)
     else:
         if rays_per_gpu:
             full = sweeps.sweep_2d(max(1, rays_per_gpu // 250) * world, 250)
@@ -73,12 +86,19 @@ def make_launch(workload, world, rank, rays_per_gpu=0):
     return np.ascontiguousarray(full[:, sweeps.partition_indices(n_total, rank, world, PARTITION)]), n_total
 
 
+MAXITERS_OVERRIDE = 0
+
+
 def solver_kwargs(workload, slice_attempts=0):
     """Solver options of the named config."""
-    if workload == "cfg3":  # RayTrace_3D.jl:395 defaults
+    if IS3D[workload]:  # RayTrace_3D.jl:395 defaults
         kw = dict(adaptive=1, reltol=1e-3, abstol=1e-6, dtmax=0.0, dtmin=0.0, maxiters=100000, t1=5.0e9, r_esc=10 * RE)
+    elif workload == "cfg4":  # scratch.jl:390 tspan, RayTrace_lat.jl:338 tolerances, maxiters 10^6 (SURVEY.md §8d)
+        kw = dict(adaptive=1, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, maxiters=1000000, t1=5.0e10, r_esc=10 * RE)
     else:  # RayTrace_lat.jl:338
         kw = dict(adaptive=1, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, maxiters=100000, t1=5.0e9, r_esc=10 * RE)
+    if MAXITERS_OVERRIDE:
+        kw["maxiters"] = MAXITERS_OVERRIDE
     if slice_attempts:
         kw["slice_attempts"] = slice_attempts
     return kw
@@ -140,20 +160,27 @@ def cpu_oracle_run(workload, launch, nthreads):
     kw = solver_kwargs(workload)
     kw.pop("adaptive")
     o = O.opts(**kw)
-    E = O.env(O.RAY3D if workload == "cfg3" else O.LAT2D)
+    E = O.env(O.RAY3D if IS3D[workload] else O.LAT2D)
     t = time.perf_counter()
-    out = O.solve_batch(E, o, launch, workload == "cfg3", nthreads)
+    out = O.solve_batch(E, o, launch, IS3D[workload], nthreads)
     dt = time.perf_counter() - t
     return dt, int(out["nfe"].astype(np.int64).sum()), launch.shape[1]
 
 
 def cpu_sample(workload, launch, nrays):
-    """A bounded, strided (hence representative) sample of the rank-0 launch list."""
+    """A bounded sample of the rank-0 launch list: ray k * 49999 mod n (a stride coprime to the sweeps' grid sizes, so
+    that every wave-normal angle, longitude and latitude is drawn — an even stride lands on 2 of cfg3's 100 angles)."""
     n = launch.shape[1]
     if nrays >= n:
         return launch
-    idx = np.linspace(0, n - 1, nrays).astype(np.int64)
+    stride = 49999
+    while np.gcd(stride, n) != 1:
+        stride += 2
+    idx = (np.arange(nrays, dtype=np.int64) * stride) % n
     return np.ascontiguousarray(launch[:, idx])
+
+
+CPU_SAMPLE_DEFAULT = {"cfg3": 40000, "cfg5": 40000, "cfg2": 96, "cfg4": 32}
 
 
 def run_reference(args, rank, world):
@@ -163,7 +190,7 @@ def run_reference(args, rank, world):
         return
     launch, _ = make_launch(args.workload, 1, 0, args.rays_per_gpu)
     ncores = os.cpu_count() or 1
-    nsample = args.cpu_sample or (40000 if args.workload == "cfg3" else 96)
+    nsample = args.cpu_sample or CPU_SAMPLE_DEFAULT[args.workload]
     sample = cpu_sample(args.workload, launch, nsample)
     for _ in range(min(args.warmup, 1)):
         cpu_oracle_run(args.workload, cpu_sample(args.workload, launch, max(64, nsample // 20)), ncores)
@@ -174,23 +201,25 @@ def run_reference(args, rank, world):
         tot_nfe += nfe
         tot_rays += nr
     val = tot_nfe / tot_t
-    desc = f"{sample.shape[1]} rays strided from the {launch.shape[1]}-ray {args.workload} launch list per step"
+    desc = f"{sample.shape[1]} rays (index k * 49999 mod n) of the {launch.shape[1]}-ray {args.workload} launch list per step"
     line = {
         "impl": "reference", "metric": "rhs_evals_per_s", "value": val, "unit": "RHS evals/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": SCALING[args.workload], "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "rays_per_s": tot_rays / tot_t,
         "config": {"workload": args.workload, "rays_per_step": int(sample.shape[1]), "solver": solver_kwargs(args.workload)},
         "cpu_baseline": {"value": val, "unit": "RHS evals/s", "cores": ncores, "kind": "port", "sample": desc},
         "e2e": {"value": val, "unit": "RHS evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference is Julia (no julia binary here); this is the plain-C oracle port, which calls the "
-                "refractive index 12x per RHS exactly as RayTrace_3D.jl does",
+                "refractive index 12x (3D) / 9x (2D) per RHS exactly as the .jl files do",
     }
     print(json.dumps(line), flush=True)
 
 
 def main():
+    global MAXITERS_OVERRIDE
     args = parse()
+    MAXITERS_OVERRIDE = args.maxiters
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -217,7 +246,7 @@ def main():
 
     launch_h, n_total = make_launch(args.workload, world, rank, args.rays_per_gpu)
     ncol, n = launch_h.shape
-    is3d = args.workload == "cfg3"
+    is3d = IS3D[args.workload]
     dim = 7 if is3d else 4
     rt = R.RayTracer("ray3d" if is3d else "lat2d", device=local_rank)
     rt.set_solver(**solver_kwargs(args.workload, args.slice))
@@ -310,8 +339,13 @@ def main():
         e2e_ms += 1e3 * (time.perf_counter() - t0)
     barrier()
     # the host-pointer path (early result copy + late patch) must deliver what the device-resident path delivered
-    if int(res_h.nfe.astype(np.int64).sum()) != nfe_local or not np.array_equal(res_h.status, status_h):
-        raise RuntimeError("e2e results differ from the device-resident solve")
+    dev_res = {"u_end": u_end, "t_end": t_end, "group_delay": gd, "status": ints[0], "naccept": ints[1],
+               "nreject": ints[2], "nfe": ints[3], "nreflect": ints[4]}
+    for name, tens in dev_res.items():  # every record, bit for bit (NaN == NaN)
+        a, b = getattr(res_h, name), tens.cpu().numpy()
+        if not np.array_equal(a.view(np.uint64) if a.dtype == np.float64 else a,
+                              b.view(np.uint64) if b.dtype == np.float64 else b):
+            raise RuntimeError(f"e2e results differ from the device-resident solve in {name}")
     h2d = ncol * n * 8
     d2h = (dim + 2) * n * 8 + 5 * n * 4
 
@@ -334,12 +368,13 @@ def main():
         K = args.steps
         value = nfe_all * K / (ms_all * 1e-3)
         flop = FLOP_PER_RHS[args.workload]
-        # dominant kernel = rt_integrate_kernel: rank-0 figures, CUDA events inside the library on the launch stream
-        achieved = (nfe_local * K * flop) / (integ_ms * 1e-3) / 1e12
+        # dominant kernel = rt_integrate_kernel (> 99 % of the step): algorithmic FLOP of rank 0's step over rank 0's
+        # WHOLE step time (init kernel, every integrate slice, group-delay kernel, scheduling gaps)
+        achieved = (nfe_local * K * flop) / (ms_local * 1e-3) / 1e12
         ncores = os.cpu_count() or 1
         cpu = None
         if world == 1 or True:
-            nsample = args.cpu_sample or (40000 if is3d else 96)
+            nsample = args.cpu_sample or CPU_SAMPLE_DEFAULT[args.workload]
             sample = cpu_sample(args.workload, launch_h, nsample)
             cdt, cnfe, cn = cpu_oracle_run(args.workload, sample, ncores)
             cpu = {"value": cnfe / cdt, "unit": "RHS evals/s", "cores": ncores, "kind": "port",
@@ -348,23 +383,24 @@ def main():
         uniq, cnt = np.unique(status_h, return_counts=True)
         line = {
             "metric": "rhs_evals_per_s", "value": value, "unit": "RHS evals/s", "n_gpus": world, "steps": K,
-            "warmup": args.warmup, "ms_per_step": ms_all / K, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms_all / K, "higher_is_better": True, "scaling": SCALING[args.workload],
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "rays_per_s": rays_all * K / (ms_all * 1e-3),
             "config": {"workload": args.workload, "rays_total": int(rays_all), "rays_per_gpu": int(n),
                        "rhs_evals_per_step": int(nfe_all), "solver": solver_kwargs(args.workload, args.slice),
-                       "partition": f"{PARTITION} x{world}", "l2": "flushed between timed steps (256 MiB fill)",
+                       "cut_off": bool(args.maxiters), "partition": f"{PARTITION} x{world}", "l2": "flushed between timed steps (256 MiB fill)",
                        "status_counts_rank0": {R.STATUS_NAMES[int(a)]: int(b) for a, b in zip(uniq, cnt)}},
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak / 1e12, "unit": "TFLOP/s",
                          "frac": achieved / (peak / 1e12), "traffic": NCU_DRAM_BYTES_PER_FULL_LAUNCH[args.workload],
-                         "traffic_note": "bytes per full-list launch (ncu, profiles/r1_ncu_integrate_v3.md); "
-                                         "0.09 TB/s: HBM is not the bound",
+                         "traffic_note": "bytes per full-list launch of the 10^6-ray list (ncu --set full, "
+                                         "profiles/r1_ncu_integrate_v3.md); 0.09 TB/s: HBM is not the bound",
                          "steady_state": None if steady is None else dict(
                              steady, achieved=steady["rhs_evals_per_s"] * flop / 1e12,
                              frac=steady["rhs_evals_per_s"] * flop / peak),
                          "peak_source": "DFMA-chain microbenchmark in this run (MEASURED_PEAKS.json has no FP64 entry)",
                          "flop_per_rhs": flop, "kernel": "rt_integrate_kernel",
-                         "avg_launch_ms": integ_ms / max(slices, 1), "launches": int(slices)},
+                         "how": "rhs_evals_per_step x flop_per_rhs / ms_per_step of rank 0 (whole step)",
+                         "integrate_span_ms_per_step": integ_ms / K, "launches": int(slices)},
             "cpu_baseline": cpu,
             "e2e": {"value": nfe_all * K / (e2e_all * 1e-3), "unit": "RHS evals/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_all / K,

@@ -90,7 +90,9 @@ typedef struct rt_solver_opts {
   int32_t slice_attempts;/* step attempts per kernel launch between compactions (0 = default 4) */
   int32_t coop_threshold;/* live-ray count at or below which 3 lanes share one ray (0 = default 10000, < 0 = never) */
   int32_t single_chain;  /* 0 = rays that start upward run as a separate, prioritised chain of launches; 1 = one chain */
-  int32_t reserved;
+  int32_t nan_policy;    /* non-finite error estimate of a step attempt: 0 = reject, shrink the step by qmin = 1/5 and retry
+                            ([EXT]; ends with DT_LESS_THAN_MIN); 1 = end the ray with RT_DT_NAN at once, which is
+                            what OrdinaryDiffEq's reject path does (dt / min(5, NaN) = NaN -> retcode DtNaN) */
 } rt_solver_opts;
 
 /* Caller-allocated structure-of-arrays result.  dim = 4 (2D) or 7 (3D). */

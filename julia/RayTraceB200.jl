@@ -17,7 +17,7 @@ mutable struct SolverOpts   # rt_solver_opts
     adaptive::Int32; save_mode::Int32; max_samples::Int32; save_stride::Int32
     maxiters::Int64; t1::Float64; dt::Float64; reltol::Float64; abstol::Float64
     dtmax::Float64; dtmin::Float64; r_esc::Float64; slice_attempts::Int32; coop_threshold::Int32
-    single_chain::Int32; reserved::Int32
+    single_chain::Int32; nan_policy::Int32
 end
 
 struct Result         # rt_result: caller-allocated arrays

@@ -44,7 +44,7 @@ class SolverOpts(C.Structure):
         ("adaptive", C.c_int32), ("save_mode", C.c_int32), ("max_samples", C.c_int32), ("save_stride", C.c_int32),
         ("maxiters", C.c_int64), ("t1", C.c_double), ("dt", C.c_double), ("reltol", C.c_double),
         ("abstol", C.c_double), ("dtmax", C.c_double), ("dtmin", C.c_double), ("r_esc", C.c_double),
-        ("slice_attempts", C.c_int32), ("coop_threshold", C.c_int32), ("single_chain", C.c_int32), ("reserved", C.c_int32),
+        ("slice_attempts", C.c_int32), ("coop_threshold", C.c_int32), ("single_chain", C.c_int32), ("nan_policy", C.c_int32),
     ]
 
 

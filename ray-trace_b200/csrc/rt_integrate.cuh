@@ -31,7 +31,7 @@
 
 struct RtDevOpts {
   int adaptive, save_mode, max_samples, save_stride;
-  int maxiters;
+  int maxiters, nan_policy;
   double t1, dt, reltol, abstol, dtmax, dtmin, r_esc;
 };
 
@@ -68,7 +68,7 @@ __constant__ double RT_BT[7] = {-0.00178001105222577714, -0.0008164344596567469,
                                 0.015151515151515152};
 
 // dense-output weights b_i(theta) of the free 4th-order interpolant
-__device__ __forceinline__ void rt_dense_weights(double th, double *b) {
+__host__ __device__ __forceinline__ void rt_dense_weights(double th, double *b) {
   double th2 = th * th;
   b[0] = ((-1.0530884977290216 * th) * (th - 1.3299890189751412)) *
          ((th2 - 1.4364028541716351 * th) + 0.7139816917074209);
@@ -78,6 +78,23 @@ __device__ __forceinline__ void rt_dense_weights(double th, double *b) {
   b[4] = ((47.37952196281928122 * (th - 1.203071208372362603)) * (th - 0.658047292653547382)) * th2;
   b[5] = ((-34.87065786149660974 * (th - 1.2)) * (th - 0.666666666666666667)) * th2;
   b[6] = ((2.5 * (th - 1.0)) * (th - 0.6)) * th2;
+}
+
+// ContinuousCallback's interior safety check (default interp_points = 10: Theta = i/9, i = 1..8, evaluated when the end
+// point shows no sign change; DiffEqBase determine_event_occurance).  The weights b_q(i/9) are evaluated once on the
+// host with rt_dense_weights (same operations as the oracle's) and uploaded by rt_create.
+__constant__ double RT_BI[8][7];
+struct RtScanIn { double k[7], u0, h, re, g0; };
+// first i in 1..8 with a strict sign change of r(Theta_i) - re against g0, 0 if none (out of line: rare)
+__device__ __noinline__ int rt_event_scan(RtScanIn in) {
+  for (int ip = 0; ip < 8; ip++) {
+    double s = RT_BI[ip][0] * in.k[0];
+#pragma unroll
+    for (int q = 1; q < 7; q++) s = s + RT_BI[ip][q] * in.k[q];
+    const double gi = (in.u0 + in.h * s) - in.re;
+    if ((in.g0 > 0.0 && gi < 0.0) || (in.g0 < 0.0 && gi > 0.0)) return ip + 1;
+  }
+  return 0;
 }
 
 // ---- the right-hand side as the kernels call it -----------------------------------------------------
@@ -375,6 +392,7 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
     status = S.status[i];
   }
   bool running = valid && status == RT_RUNNING, hit = false;
+  double hit_hi = 1.0;  // upper end of the event bracket in Theta
   RtExtras2D ex = {0, 0, 0, 0};
 
   for (int a = 0; a < attempts; a++) {
@@ -456,6 +474,7 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
       if (!(EEst <= 1.0)) {  // reject (NaN included)
         nreject++;
         if (EEst != EEst) {
+          if (O.nan_policy == 1) { status = RT_DT_NAN; running = false; continue; }  // OrdinaryDiffEq: dt = NaN -> DtNaN
           h = h * 0.2;
         } else {
           double qq = rt_pow_dev(EEst, 0.14) / 0.9;
@@ -468,6 +487,7 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
       q = q / 0.9;
       if (q > 5.0) q = 5.0;
       if (q < 0.1) q = 0.1;
+      if (q >= 1.0 && q <= 1.2) q = 1.0;  // qsteady_min <= q <= qsteady_max: the accepted step keeps dt
       qold = (EEst > 1e-4) ? EEst : 1e-4;
       hnew = h / q;
     }
@@ -493,6 +513,30 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
         running = false;
         continue;
       }
+      if (g0 != 0.0) {
+        // interior safety check, filtered: sum_q b_q(Theta) = Theta, so r(Theta) - re = g0 + h Theta k_1 + E with
+        // |E| <= 7.59 |h| max_q |k_q - k_1| (max over Theta of sum_q |b_q| = 7.582); no sign change is possible while
+        // |g0| exceeds |h| (|k_1| + 8 sum_q |k_q - k_1|) by more than the evaluation's rounding (1 mm + 1e-12 |r|).
+        // Otherwise the eight points are evaluated exactly as the oracle does (which always evaluates them).
+        const double k10 = RT_K(0, 0);
+        double dev = rt_abs(RT_K(1, 0) - k10);
+#pragma unroll
+        for (int q = 2; q < 7; q++) dev = dev + rt_abs(RT_K(q, 0) - k10);
+        const double reach = rt_abs(h) * (rt_abs(k10) + 8.0 * dev) + (1.0e-3 + 1.0e-12 * rt_abs(u[0]));
+        if (!(rt_abs(g0) > reach)) {
+          RtScanIn in;
+#pragma unroll
+          for (int q = 0; q < 7; q++) in.k[q] = RT_K(q, 0);
+          in.u0 = u[0]; in.h = h; in.re = E.re; in.g0 = g0;
+          const int ip = rt_event_scan(in);
+          if (ip > 0) {
+            hit = true;
+            hit_hi = (double)ip / 9.0;
+            running = false;
+            continue;
+          }
+        }
+      }
     }
     t = tn;
 #pragma unroll
@@ -514,7 +558,7 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
 
   if (hit) {  // re_cb's root: bisection on the step's dense output (u, h and the seven stages are those of the step)
     const double g0 = u[0] - E.re;
-    double lo = 0.0, hi = 1.0, b[7];
+    double lo = 0.0, hi = hit_hi, b[7];
     for (int it = 0; it < 52; it++) {
       double mid = 0.5 * (lo + hi);
       rt_dense_weights(mid, b);

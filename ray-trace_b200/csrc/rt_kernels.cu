@@ -234,6 +234,7 @@ static RtDevOpts make_dev_opts(const rt_solver_opts &o) {
   d.save_stride = o.save_stride > 0 ? o.save_stride : 1;
   long long mi = o.maxiters > 0 ? o.maxiters : 100000;
   d.maxiters = mi > 2000000000LL ? 2000000000 : (int)mi;
+  d.nan_policy = o.nan_policy;
   d.t1 = o.t1;
   d.dt = o.dt;
   d.reltol = o.reltol;
@@ -286,6 +287,11 @@ extern "C" int rt_create(rt_ctx **out, int device) {
     RT_CUDA(ctx, cudaMalloc(&ctx->late_d, RT_LATE_CAP * 9 * sizeof(double)));
     RT_CUDA(ctx, cudaMallocHost(&ctx->late_hi, RT_LATE_CAP * 5 * sizeof(int)));
     RT_CUDA(ctx, cudaMallocHost(&ctx->late_hd, RT_LATE_CAP * 9 * sizeof(double)));
+  }
+  {  // interior event-check weights b_q(i/9), host-evaluated (rt_integrate.cuh: RT_BI)
+    double bi[8][7];
+    for (int ip = 0; ip < 8; ip++) rt_dense_weights((double)(ip + 1) / 9.0, bi[ip]);
+    RT_CUDA(ctx, cudaMemcpyToSymbol(RT_BI, bi, sizeof(bi)));
   }
   rt_env_preset(RT_PRESET_LAT2D, &ctx->env);
   rt_solver_preset(RT_PRESET_LAT2D, &ctx->opts);
@@ -367,6 +373,7 @@ extern "C" int rt_set_solver(rt_ctx *ctx, const rt_solver_opts *o) {
   if (!o->adaptive && !(o->dt > 0.0)) return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: fixed-step mode needs dt > 0");
   if (o->adaptive && !(o->reltol > 0.0 || o->abstol > 0.0))
     return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: adaptive mode needs a tolerance");
+  if (o->nan_policy < 0 || o->nan_policy > 1) return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: nan_policy must be 0 or 1");
   if (o->save_mode && o->max_samples <= 0)
     return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: save_mode=1 needs max_samples > 0");
   ctx->opts = *o;
@@ -1267,15 +1274,25 @@ extern "C" int rt_debug_fallback_samples(rt_ctx *ctx, double *out, int max_rows)
 }
 
 // ---------------------------------------------------------------------------------------------------
-// FP64 roofline denominator: 8 independent DFMA chains per thread, all SMs full
+// FP64 roofline denominator: NCH independent DFMA chains per thread, every SM full.  Several shapes are timed and the
+// best rate is returned (chains x resident warps: the pipe issues one FP64 warp instruction per 2 cycles per
+// scheduler and a dependent DFMA returns after 8, so >= 4 chains in flight per scheduler saturate it; the shapes
+// differ only in how much slack they leave).  profiles/r2_dfma_peak_ncu.md has the pipe-utilisation proof.
 // ---------------------------------------------------------------------------------------------------
+template <int NCH>
 __global__ void __launch_bounds__(256) rt_dfma_peak_kernel(double *out, int iters, double a, double b) {
-  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  double x[NCH];
+#pragma unroll
+  for (int c = 0; c < NCH; c++) x[c] = (double)threadIdx.x + c;
+#pragma unroll 4
   for (int k = 0; k < iters; k++) {
-    x0 = __fma_rn(x0, a, b); x1 = __fma_rn(x1, a, b); x2 = __fma_rn(x2, a, b); x3 = __fma_rn(x3, a, b);
-    x4 = __fma_rn(x4, a, b); x5 = __fma_rn(x5, a, b); x6 = __fma_rn(x6, a, b); x7 = __fma_rn(x7, a, b);
+#pragma unroll
+    for (int c = 0; c < NCH; c++) x[c] = __fma_rn(x[c], a, b);
   }
-  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  double s = 0.0;
+#pragma unroll
+  for (int c = 0; c < NCH; c++) s += x[c];
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
 extern "C" int rt_measure_fp64_peak(rt_ctx *ctx, double *flops) {
@@ -1283,23 +1300,31 @@ extern "C" int rt_measure_fp64_peak(rt_ctx *ctx, double *flops) {
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   cudaDeviceProp prop;
   RT_CUDA(ctx, cudaGetDeviceProperties(&prop, ctx->device));
-  const int blocks = prop.multiProcessorCount * 8, iters = 1 << 14;
+  const int max_blocks = prop.multiProcessorCount * 8;
   double *d = nullptr;
-  RT_CUDA(ctx, cudaMalloc(&d, (size_t)blocks * 256 * sizeof(double)));
+  RT_CUDA(ctx, cudaMalloc(&d, (size_t)max_blocks * 256 * sizeof(double)));
   double best = 0.0;
-  for (int rep = 0; rep < 5; rep++) {
-    cudaEventRecord(ctx->ev[0], ctx->stream);
-    rt_dfma_peak_kernel<<<blocks, 256, 0, ctx->stream>>>(d, iters, 0.9999999, 1e-7);
-    cudaEventRecord(ctx->ev[1], ctx->stream);
-    cudaError_t e = cudaStreamSynchronize(ctx->stream);
-    if (e != cudaSuccess) {
-      cudaFree(d);
-      return set_err(ctx, RT_ERR_CUDA, "rt_measure_fp64_peak: %s", cudaGetErrorString(e));
+  // shape = (chains per thread, blocks of 256 threads per SM); each launch is ~2 ms of DFMAs
+  const int shapes[4][2] = {{8, 8}, {8, 4}, {16, 4}, {4, 8}};
+  for (int sh = 0; sh < 4; sh++) {
+    const int nch = shapes[sh][0], blocks = prop.multiProcessorCount * shapes[sh][1];
+    const int iters = (1 << 20) / (nch * shapes[sh][1]);
+    for (int rep = 0; rep < 4; rep++) {
+      cudaEventRecord(ctx->ev[0], ctx->stream);
+      if (nch == 4) rt_dfma_peak_kernel<4><<<blocks, 256, 0, ctx->stream>>>(d, iters, 0.9999999, 1e-7);
+      else if (nch == 8) rt_dfma_peak_kernel<8><<<blocks, 256, 0, ctx->stream>>>(d, iters, 0.9999999, 1e-7);
+      else rt_dfma_peak_kernel<16><<<blocks, 256, 0, ctx->stream>>>(d, iters, 0.9999999, 1e-7);
+      cudaEventRecord(ctx->ev[1], ctx->stream);
+      cudaError_t e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess) {
+        cudaFree(d);
+        return set_err(ctx, RT_ERR_CUDA, "rt_measure_fp64_peak: %s", cudaGetErrorString(e));
+      }
+      float ms = 0;
+      cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+      const double fl = 2.0 * nch * (double)iters * (double)blocks * 256.0 / (ms * 1e-3);
+      if (rep > 0 && fl > best) best = fl;
     }
-    float ms = 0;
-    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
-    double fl = 2.0 * 8.0 * (double)iters * (double)blocks * 256.0 / (ms * 1e-3);
-    if (rep > 0 && fl > best) best = fl;
   }
   cudaFree(d);
   *flops = best;

@@ -42,7 +42,7 @@ class SolverOpts(C.Structure):
         ("slice_attempts", C.c_int32),
         ("coop_threshold", C.c_int32),
         ("single_chain", C.c_int32),
-        ("reserved", C.c_int32),
+        ("nan_policy", C.c_int32),
     ]
 
 
@@ -63,6 +63,7 @@ def lib():
         for n in ("orc_ddr_2d", "orc_ddlam_2d", "orc_ddchi_2d", "orc_ddf_2d", "orc_dd_3d", "orc_ddrho_3d",
                   "orc_plasmasphere_eq", "orc_diffusive_equilibrium", "orc_ionosphere_eq", "orc_L_rlam"):
             getattr(_lib, n).restype = C.c_double
+        _lib.orc_interior_events.restype = C.c_longlong
         assert _lib.orc_sizeof_env() == C.sizeof(OrcEnv)
     return _lib
 
@@ -74,9 +75,9 @@ def env(preset=LAT2D):
 
 
 def opts(adaptive=1, t1=5.0e9, dt=0.0, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, maxiters=100000,
-         r_esc=0.0, save_mode=0, max_samples=0, save_stride=1, slice_attempts=0):
+         r_esc=0.0, save_mode=0, max_samples=0, save_stride=1, slice_attempts=0, nan_policy=0):
     return SolverOpts(adaptive, save_mode, max_samples, save_stride, maxiters, t1, dt, reltol, abstol, dtmax,
-                      dtmin, r_esc, slice_attempts, 0, 0, 0)
+                      dtmin, r_esc, slice_attempts, 0, 0, nan_policy)
 
 
 def _d(x):
@@ -181,6 +182,12 @@ def solve_test_ode(which, o, u0, t0=0.0, re_evt=0.0, cap=0):
     lib().orc_solve_test_ode(C.c_int(which), C.byref(o), _p(u0), _d(t0), _d(re_evt), _p(ue), C.byref(te),
                              _p(ints), _p(traj) if cap else None, C.c_int64(cap), C.byref(ns))
     return RayOut(ue, te.value, ints, traj[: ns.value] if cap else None)
+
+
+def interior_events(reset=False):
+    """Events the oracle located through ContinuousCallback's interior safety check (Theta = i/9) since the last reset
+    (single-thread runs only)."""
+    return int(lib().orc_interior_events(C.c_int(int(reset))))
 
 
 MATH = {"exp": 0, "exp10": 1, "log": 2, "log10": 3, "sin": 4, "cos": 5, "tan": 6, "atan": 7, "acos": 8, "pow_m4p5": 9}

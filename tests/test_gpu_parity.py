@@ -443,7 +443,7 @@ def test_cfg3_full_size_properties_and_partition():
     fb = (C.c_ulonglong * 8)()
     R.api._lib().rt_debug_fallback_counts(rt._ctx, fb, 1)
     assert set(np.unique(res.status)) == {2}  # every ray of this sweep ends on the Earth
-    assert int(res.nfe.astype(np.int64).sum()) == 285546464  # the workload bench.py quotes
+    assert int(res.nfe.astype(np.int64).sum()) == 301445828  # the workload bench.py quotes (the oracle run over the full list gives the same)
     assert np.array_equal(res.nfe, 6 * (res.naccept + res.nreject) + 2)
     assert np.max(np.abs(res.u_end[0] - RE)) < 1e-6 and np.all(res.t_end > 0)  # metres: bisection to 1 ulp in theta
     assert _same(res.group_delay, res.u_end[6])

@@ -46,6 +46,41 @@ def test_event_fires_on_upward_crossing_too():
     assert r.status == 2 and abs(r.t_end - math.pi / 6) < 1e-6 and r.u_end[0] <= 0.5
 
 
+def test_event_inside_a_step_is_found_by_the_interior_check():
+    """ContinuousCallback's default interp_points = 10: a step whose end points are both on the same side but which
+    dips through the level in between still terminates (DiffEqBase determine_event_occurance).  -cos(t) is above 0.99
+    only for 3.0001 < t < 3.2831, inside the fixed step [2.8, 3.5]."""
+    O.interior_events(reset=True)
+    o = O.opts(adaptive=0, dt=0.7, t1=7.0, maxiters=100)
+    r = O.solve_test_ode(0, o, [-1.0, 0.0], re_evt=0.99)
+    assert r.status == 2 and O.interior_events() == 1
+    assert abs(r.t_end - math.acos(-0.99)) < 2e-3 and r.u_end[0] <= 0.99  # 4th-order interpolant on a 0.7-long step
+    assert r.naccept == 5
+    # the same level is never reached from a launch exactly on it with zero initial sign (prev_sign = 0: no event)
+    r = O.solve_test_ode(0, O.opts(adaptive=0, dt=0.1, t1=1.0, maxiters=100), [0.99, 0.0], re_evt=0.99)
+    assert r.status == 1
+
+
+def test_controller_deadband_keeps_the_step():
+    """step_accept_controller!: 1 <= q <= 1.2 (qsteady_min, qsteady_max) leaves dt unchanged; on a smooth problem at
+    steady state consecutive accepted steps therefore repeat the same dt exactly."""
+    o = O.opts(reltol=1e-6, abstol=1e-6, dtmax=0, dtmin=0, t1=50.0)
+    r = O.solve_test_ode(0, o, [1.0, 0.0], cap=4096)
+    dt = np.diff(r.traj[:, 0])
+    assert r.status == 1 and np.count_nonzero(dt[1:-1] == dt[:-2]) > 0.3 * dt.size
+
+
+def test_nan_policy():
+    """A non-finite error estimate: nan_policy 0 retries with dt/5 (ends with DtLessThanMin), 1 ends with DtNaN."""
+    E = O.env(O.RAY3D)
+    u0 = [E.re + 1e6, math.pi / 4, 0.0, 1.0, 1.0, 1.0e-3, 0.0]
+    kw = dict(reltol=1e-3, dtmax=0, dtmin=0, dt=1.0e12, t1=5e12)  # a first step far below the centre: NaN stages
+    r0 = O.solve_ray_3d(E, O.opts(**kw), u0, 1000.0)
+    r1 = O.solve_ray_3d(E, O.opts(nan_policy=1, **kw), u0, 1000.0)
+    assert r1.status == 7 and r1.nreject == 1 and r1.naccept == 0
+    assert r0.nreject >= 1 and r0.status != 7
+
+
 def test_maxiters_dtmin_and_escape_classes():
     o = O.opts(reltol=1e-6, dtmax=0, dtmin=0, t1=100.0, maxiters=10)
     r = O.solve_test_ode(1, o, [1.0, 0.0, 0.0])
