@@ -295,6 +295,10 @@ def main():
     ms_local = sum(a.elapsed_time(b) for a, b in ev)
     nfe_local = int(ints[3].to(torch.int64).sum().item())
     status_h = ints[0].cpu().numpy()
+    # the device-resident step's records, kept for the comparison with the host-pointer path below
+    dev_res = {"u_end": u_end.cpu().numpy(), "t_end": t_end.cpu().numpy(), "group_delay": gd.cpu().numpy(),
+               "status": status_h, "naccept": ints[1].cpu().numpy(), "nreject": ints[2].cpu().numpy(),
+               "nfe": ints[3].cpu().numpy(), "nreflect": ints[4].cpu().numpy()}
     # diagnostic, outside the timed region: the integrate kernel in steady state (every ray alive, full lists):
     # the same sweep cut off after 24 step attempts, one chain
     steady = None
@@ -339,10 +343,8 @@ def main():
         e2e_ms += 1e3 * (time.perf_counter() - t0)
     barrier()
     # the host-pointer path (early result copy + late patch) must deliver what the device-resident path delivered
-    dev_res = {"u_end": u_end, "t_end": t_end, "group_delay": gd, "status": ints[0], "naccept": ints[1],
-               "nreject": ints[2], "nfe": ints[3], "nreflect": ints[4]}
-    for name, tens in dev_res.items():  # every record, bit for bit (NaN == NaN)
-        a, b = getattr(res_h, name), tens.cpu().numpy()
+    for name, b in dev_res.items():  # every record, bit for bit (NaN == NaN)
+        a = getattr(res_h, name)
         if not np.array_equal(a.view(np.uint64) if a.dtype == np.float64 else a,
                               b.view(np.uint64) if b.dtype == np.float64 else b):
             raise RuntimeError(f"e2e results differ from the device-resident solve in {name}")

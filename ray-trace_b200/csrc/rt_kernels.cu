@@ -730,7 +730,12 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   S.traj = ctx->traj;
   cudaStream_t st = ctx->stream;
   const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
-  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // the long rays' one-thread-per-ray launches may ask for more shared memory than they use, so that an SM hosting one
+  // of their blocks takes fewer bulk blocks beside it (see the chain loop)
+  static const long long prio_smem_kb = getenv("RT_PRIO_SMEM_KB") ? atoll(getenv("RT_PRIO_SMEM_KB")) : 0;
+  static const long long prio_smem_rays = getenv("RT_PRIO_SMEM_RAYS") ? atoll(getenv("RT_PRIO_SMEM_RAYS")) : 19000;
+  const size_t smem_prio = (size_t)prio_smem_kb * 1024 > smem ? (size_t)prio_smem_kb * 1024 : smem;
+  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_prio));
   RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
@@ -829,6 +834,8 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
           const long long before = C.upper;
           C.upper = *C.h;
           if (adapt) C.att = (C.upper * 100 >= before * 97) ? (C.att * 2 > 64 ? 64 : C.att * 2) : attempts;
+          static const int dieoff_att = getenv("RT_DIEOFF_ATT") ? atoi(getenv("RT_DIEOFF_ATT")) : 0;
+          if (adapt && dieoff_att > 0 && C.upper * 100 < before * 90) C.att = dieoff_att;
           if (dbg) {
             float ms = 0;
             cudaEventRecord(ctx->ev[2], C.st);
@@ -882,7 +889,11 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         const long long all = ch[0].upper + ch[1].upper + ch[2].upper + ch[3].upper;
         static const int policy = getenv("RT_COOP_POLICY") ? atoi(getenv("RT_COOP_POLICY")) : 1;
         static const long long coop_sum = getenv("RT_COOP_SUM") ? atoll(getenv("RT_COOP_SUM")) : 25000;
-        const bool coop = C.upper <= coop_threshold && (policy == 0 || all <= coop_threshold + coop_sum);
+        // developer switch: the priority chains also go cooperative while their attempt count is inside a window
+        static const long long win_lo = getenv("RT_COOP_WIN_LO") ? atoll(getenv("RT_COOP_WIN_LO")) : 0;
+        static const long long win_hi = getenv("RT_COOP_WIN_HI") ? atoll(getenv("RT_COOP_WIN_HI")) : 0;
+        const bool in_window = (c & 1) && C.nominal >= win_lo && C.nominal < win_hi;
+        const bool coop = C.upper <= coop_threshold && (policy == 0 || in_window || all <= coop_threshold + coop_sum);
         // a launch of the priority chain has to wait for blocks of the other chain to retire before it gets SM
         // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
         static const int coop_att = getenv("RT_COOP_ATT") ? atoi(getenv("RT_COOP_ATT")) : 32;
@@ -899,7 +910,8 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           else
-            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
+            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK,
+                                               ((c & 1) && ch[1].upper + ch[3].upper <= prio_smem_rays) ? smem_prio : smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           C.cur ^= 1;

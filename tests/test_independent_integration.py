@@ -1,0 +1,85 @@
+"""Whole rays against an integration that shares nothing with the oracle's integrator.
+
+tests/golden/integration_rk45.json holds cfg1 (the reference's own ray, RayTrace_lat.jl:333-338) and ten rays of the
+cfg3 grid (RayTrace_3D.jl:390-395), two of them long magnetospheric paths, integrated by scipy's RK45 (Dormand-Prince:
+another tableau, another step controller, another event root-finder) at rtol 1e-8 over the independent pure-Python
+right-hand sides of tools/make_golden.py (`python tools/make_golden.py --integrate`, ~2 min).  The oracle's Tsit5
+restatement, run at the same tight tolerance, has to land on the same event time / end state: this pins the signs of
+du, the slot-4 dual use, the event direction and the group delay THROUGH the integrator.  The bound is the reference's
+own finite-difference noise (integrators agree to ~1e-3 in r at worst), far above what is observed
+(1e-5).  At the bench's own tolerance (reltol 1e-3, the library default at RayTrace_3D.jl:395) the short rays agree
+to that tolerance; the long paths do not converge at 1e-3 in any integrator (they are sensitive to the 1e-11-wide
+differences' rounding noise), which is a property of the reference's call, recorded here, not a parity criterion.
+"""
+import json
+import math
+import os
+
+import numpy as np
+
+import oracle_lib as O
+
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "integration_rk45.json")))
+RE = 6.3712e6
+
+
+def _close(a, b, rtol, atol):
+    a, b = np.asarray(a, dtype=float), np.asarray(b, dtype=float)
+    return bool(np.all(np.abs(a - b) <= atol + rtol * np.abs(b)))
+
+
+def test_cfg1_reference_ray_against_scipy_rk45():
+    g = GOLD["cfg1"]
+    E = O.env(O.LAT2D)
+    assert not g["out"]["event"] and g["out"]["t"] == 5.0e9  # the ray is still aloft at tspan's end
+    # the reference's own options (RayTrace_lat.jl:338: reltol 1e-7, dtmax 1e6, dtmin 1e-8)
+    r = O.solve_ray_2d(E, O.opts(), g["u0"])
+    assert r.status == 1 and r.t_end == 5.0e9
+    assert _close(r.u_end[:3], g["out"]["y"][:3], 2e-6, 0.0), (r.u_end, g["out"]["y"])
+    # slot 4 = f0 + group delay (RayTrace_lat.jl:257,273): 0.36 s after 5e9 path units, same to 1e-7 relative
+    gd, gd_ref = r.u_end[3] - g["u0"][3], g["out"]["y"][3] - g["u0"][3]
+    assert 0.3 < gd_ref < 0.4 and abs(gd - gd_ref) < 1e-6 * gd_ref
+    # tighter still
+    r = O.solve_ray_2d(E, O.opts(reltol=1e-9, abstol=1e-9, dtmax=0, dtmin=0), g["u0"])
+    assert r.status == 1 and _close(r.u_end[:3], g["out"]["y"][:3], 5e-6, 0.0)  # 2.2e-6 observed: finite-difference noise
+
+
+def test_cfg3_rays_against_scipy_rk45_at_matched_tolerance():
+    E = O.env(O.RAY3D)
+    worst_t = worst_y = 0.0
+    for ray in GOLD["cfg3"]:
+        g = ray["out"]
+        assert g["event"] and abs(g["y"][0] - RE) < 1e-3  # every ray of this grid comes down to the surface
+        r = O.solve_ray_3d(E, O.opts(reltol=1e-8, abstol=1e-10, dtmax=0, dtmin=0, maxiters=10 ** 7), ray["u0"], ray["freq"])
+        assert r.status == 2, ray["grid_index"]  # Terminated: same class
+        assert abs(r.u_end[0] - RE) < 1e-6
+        dt = abs(r.t_end - g["t"]) / g["t"]
+        dy = np.max(np.abs(r.u_end[1:] - np.array(g["y"][1:])) / np.maximum(np.abs(g["y"][1:]), 1e-2))
+        worst_t, worst_y = max(worst_t, dt), max(worst_y, dy)
+        assert dt < 1e-4 and dy < 1e-3, (ray["grid_index"], dt, dy)
+    assert worst_t < 2e-5 and worst_y < 1e-3  # observed 6e-6 / 2e-4 (the 1e-11 differences' noise)
+
+
+def test_cfg3_short_rays_at_the_bench_tolerance():
+    E = O.env(O.RAY3D)
+    n_long = 0
+    for ray in GOLD["cfg3"]:
+        g = ray["out"]
+        r = O.solve_ray_3d(E, O.opts(reltol=1e-3, dtmax=0, dtmin=0), ray["u0"], ray["freq"])
+        assert r.status == 2
+        if r.naccept + r.nreject > 200:
+            n_long += 1  # not converged at 1e-3 by construction of the reference's call (see the module docstring)
+            continue
+        assert abs(r.t_end - g["t"]) / g["t"] < 3e-3, ray["grid_index"]
+        assert _close(r.u_end[1:3], g["y"][1:3], 2e-2, 1e-3)          # theta, phi
+        assert _close(r.u_end[6], g["y"][6], 2e-2, 0.0)               # group delay T
+    assert n_long == 2
+
+
+def test_generator_reproduces_one_fixture_row():
+    """The committed fixture is what the committed script produces (one short 3D ray, a few seconds)."""
+    import tools_golden as TG
+    ray = GOLD["cfg3"][7]
+    out = TG.integrate_independent("ray3d", ray["u0"], ray["freq"], rtol=GOLD["rtol"])
+    assert out["event"] and abs(out["t"] - ray["out"]["t"]) <= 1e-9 * ray["out"]["t"]
+    assert _close(out["y"], ray["out"]["y"], 1e-9, 1e-12)

@@ -169,3 +169,46 @@ def test_variant_presets_differ_as_the_files_do():
     du_m = O.haselgrove_2d(O.env(O.RAYMAIN), [r, th, chi, f])
     du_s = O.haselgrove_2d(O.env(O.SCRATCH), [r, th, chi, f])
     assert np.isfinite(du_m).all() and np.isfinite(du_s).all()
+
+
+# ---- the Haselgrove right-hand side against the independent restatement's goldens (tests/golden/haselgrove_rhs.json) ----
+RHS_GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "haselgrove_rhs.json")))
+EPS = 2.220446049250313e-16
+
+
+def _fd_noise(mu, nulp=48):
+    """|error| of a width-1e-11 central difference of mu when each mu carries `nulp`/2 ulp of libm disagreement."""
+    return nulp * EPS * mu / 1.0e-11
+
+
+@pytest.mark.parametrize("key,pid", [("lat2d", O.LAT2D), ("raymain", O.RAYMAIN)])
+def test_golden_haselgrove_2d(key, pid):
+    """du[1], du[2] (mu and dmu/dpsi only) at 1e-9 (dmu/dpsi's own cancellation), du[4] within the 1e-5-wide
+    difference in f's rounding noise, du[3] within the 1e-11-wide difference's rounding noise (RayTrace_lat.jl:210-222,270-273; RayMain.jl:341-344)."""
+    E = O.env(pid)
+    assert len(RHS_GOLD[key]) >= 20
+    for row in RHS_GOLD[key]:
+        u, g, mu = row["u"], row["du"], row["mu"]
+        du = O.haselgrove_2d(E, u)
+        assert rel(du[0], g[0]) < 1e-9 and rel(du[1], g[1]) < 1e-9, u
+        # (1 + (f/mu) dmu/df) / c: the 1e-5-wide difference turns nulp ulp of mu into f nulp eps / 1e-5
+        assert abs(du[3] - g[3]) <= (u[3] * 48 * EPS / 1.0e-5) / 2.99792458e8 + 1e-9 * abs(g[3]), u
+        bound = _fd_noise(mu) * abs(math.cos(u[2])) / (u[0] * mu * mu) + 1e-9 * abs(g[2])
+        assert abs(du[2] - g[2]) <= bound, (u, du[2], g[2], bound)
+        assert np.sign(du[0]) == np.sign(g[0]) and np.sign(du[1]) == np.sign(g[1])
+
+
+def test_golden_haselgrove_3d():
+    """du[1..4] and du[6] are free of noisy differences (Kimura-form d(mu)/d(rho_k); d(mu)/dr and d(mu)/dphi are
+    exactly 0); du[5] carries the 1e-11-wide theta difference, du[7] the 1e-5-wide f difference
+    (RayTrace_3D.jl:223-323,350-356)."""
+    E = O.env(O.RAY3D)
+    assert len(RHS_GOLD["ray3d"]) >= 20
+    for row in RHS_GOLD["ray3d"]:
+        u, f, g, mu = row["u"], row["freq"], row["du"], row["mu"]
+        du = O.haselgrove_3d(E, u, f)
+        for k in (0, 1, 2, 3, 5):
+            assert rel(du[k], g[k]) < 1e-8, (k, u, du[k], g[k])
+        assert abs(du[6] - g[6]) <= (f * 48 * EPS / 1.0e-5) / 2.99792458e8 + 1e-9 * abs(g[6]), u
+        bound = _fd_noise(mu) / (u[0] * mu) + 1e-8 * abs(g[4])
+        assert abs(du[4] - g[4]) <= bound, (u, du[4], g[4], bound)
