@@ -256,21 +256,17 @@ def main():
 
     # device-resident launch list and results
     launch_d = torch.from_numpy(launch_h).to(dev)
-    u_end = torch.empty((dim, n), dtype=torch.float64, device=dev)
-    t_end = torch.empty(n, dtype=torch.float64, device=dev)
-    gd = torch.empty(n, dtype=torch.float64, device=dev)
-    ints = torch.empty((5, n), dtype=torch.int32, device=dev)
-    res_ptrs = {"u_end": u_end.data_ptr(), "t_end": t_end.data_ptr(), "group_delay": gd.data_ptr(),
-                "status": ints[0].data_ptr(), "naccept": ints[1].data_ptr(), "nreject": ints[2].data_ptr(),
-                "nfe": ints[3].data_ptr(), "nreflect": ints[4].data_ptr()}
+    # the solver writes straight into the two gather buffers (doubles [dim+2, n], int32 [5, n]): no packing step
+    rec_d, ints, views = multi.alloc_terminal(n, dim, dev)
+    u_end, t_end, gd = views["u_end"], views["t_end"], views["group_delay"]
+    res_ptrs = {k: v.data_ptr() for k, v in views.items()}
     cols = [launch_d[k].data_ptr() for k in range(ncol)]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def step_device():
         st = rt.solve_device(n, cols, res_ptrs)
         if world > 1:
-            d, i = multi.pack_terminal(u_end, t_end, gd, ints[0], ints[1], ints[2], ints[3], ints[4])
-            multi.gather_terminal(d, i, n_total, rank, world, layout=PARTITION)
+            multi.gather_terminal(rec_d, ints, n_total, rank, world, layout=PARTITION)
         return st
 
     for _ in range(args.warmup):

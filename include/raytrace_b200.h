@@ -171,6 +171,46 @@ RT_API int rt_solve_3d_device(rt_ctx *ctx, int64_t n, const double *r, const dou
                               const double *rho_phi, const double *T0, const double *f,
                               const double *t0, rt_result *res);
 
+/* counters and timings of the last solve of a context (rt_get_stats, rt_multi_get_stats) */
+typedef struct rt_stats {
+  int64_t kernel_launches;   /* kernels launched by the last solve */
+  int64_t slices;            /* integrate-kernel launches of the last solve */
+  double integrate_ms;       /* CUDA-event time of the integrate kernels of the last solve */
+  double total_ms;           /* CUDA-event time of the whole last solve on the stream */
+  int64_t total_nfe;         /* sum of nfe over rays of the last solve */
+  int64_t prio_rays;         /* rays the last solve put on the priority chain */
+} rt_stats;
+
+/* ---- the same solve over several GPUs of one box, behind the same boundary ------------------- */
+/* One process (the Julia session), one context and one host thread per device.  Rays are independent
+ * (RayTrace_3D.jl:327-359 shares nothing between rays), so the launch list is partitioned inside the library —
+ * block-cyclically: blocks of `block` consecutive rays go round the devices, which spreads the expensive rays of a
+ * sweep (they cluster in launch-parameter space) and lets every column travel as ONE strided copy per device,
+ * straight between the caller's arrays and device memory.  Results arrive in the caller's arrays in launch order;
+ * there is no device-to-device exchange.  All pointers are HOST pointers (pinned arrays allow the early result copy,
+ * see rt_solve_3d).  devices = NULL means 0 .. ngpu-1; ngpu <= 0 means every visible device. */
+typedef struct rt_multi rt_multi;
+RT_API int rt_multi_create(rt_multi **m, int ngpu, const int *devices);
+RT_API void rt_multi_destroy(rt_multi *m);
+RT_API int rt_multi_count(const rt_multi *m);
+RT_API const char *rt_multi_last_error(const rt_multi *m);
+RT_API int rt_multi_set_env(rt_multi *m, const rt_env_params *env);       /* every device */
+RT_API int rt_multi_set_solver(rt_multi *m, const rt_solver_opts *opts);  /* every device */
+RT_API int rt_multi_set_block(rt_multi *m, int64_t block);                /* 0 = automatic (<= 4096 rays) */
+/* ODEProblem + solve over a launch list, RayTrace_lat.jl:333-338 / RayTrace_3D.jl:390-395, on all devices of m */
+RT_API int rt_solve_2d_multi(rt_multi *m, int64_t n, const double *r, const double *theta, const double *chi,
+                             const double *f, const double *t0, rt_result *res);
+RT_API int rt_solve_3d_multi(rt_multi *m, int64_t n, const double *r, const double *theta, const double *phi,
+                             const double *rho_r, const double *rho_theta, const double *rho_phi, const double *T0,
+                             const double *f, const double *t0, rt_result *res);
+/* the partition a solve of n rays uses: block length and rays per device (counts[rt_multi_count]); the launch-list
+ * index of device gpu's local ray; the per-device context (for rt_traj_* and rt_get_stats after a solve: trajectories
+ * stay on the device that traced them and are indexed by local ray) */
+RT_API int rt_multi_partition(rt_multi *m, int64_t n, int64_t *block, int64_t *counts);
+RT_API int64_t rt_multi_global_index(rt_multi *m, int64_t n, int gpu, int64_t local);
+RT_API rt_ctx *rt_multi_ctx(rt_multi *m, int gpu);
+RT_API int rt_multi_get_stats(const rt_multi *m, int gpu, rt_stats *stats);
+
 /* ---- trajectory output of the last solve (save_mode = 1) ------------------------------------- */
 /* columns: 2D  t, r, lam, chi, u4, mu, dmudpsi, dip, psi  (RayTrace_lat.jl:318-324,345-349) = 9
  *          3D  t, r, th, ph, rho_r, rho_th, rho_ph, T      (RayTrace_3D.jl:333)             = 8 */
@@ -187,14 +227,6 @@ RT_API int rt_traj_derived_columns(rt_ctx *ctx);
 RT_API int rt_traj_derived(rt_ctx *ctx, const int64_t *offsets, double *out);
 
 /* ---- instrumentation ------------------------------------------------------------------------- */
-typedef struct rt_stats {
-  int64_t kernel_launches;   /* kernels launched by the last solve */
-  int64_t slices;            /* integrate-kernel launches of the last solve */
-  double integrate_ms;       /* CUDA-event time of the integrate kernels of the last solve */
-  double total_ms;           /* CUDA-event time of the whole last solve on the stream */
-  int64_t total_nfe;         /* sum of nfe over rays of the last solve */
-  int64_t prio_rays;         /* rays the last solve put on the priority chain */
-} rt_stats;
 RT_API int rt_get_stats(const rt_ctx *ctx, rt_stats *stats);
 /* dependent-free DFMA throughput of this device in FLOP/s (roofline denominator) */
 RT_API int rt_measure_fp64_peak(rt_ctx *ctx, double *flops_per_s);

@@ -21,6 +21,7 @@ from . import build as _build
 __all__ = [
     "RayTracer", "ODEProblem", "ODESolution", "Tsit5", "solve", "EnvParams", "SolverOpts", "initialize_plasmasphere",
     "env_preset", "solver_preset", "read_ray_start", "write_ray_start", "STATUS_NAMES", "PRESETS", "lib_path",
+    "MultiRayTracer",
 ]
 
 PRESETS = {"lat2d": 0, "ray3d": 1, "raymain": 2, "scratch": 3}
@@ -294,6 +295,85 @@ class RayTracer:
             if derived:  # Cartesian track and step sizes, computed on the device (RayTrace_lat.jl:351-352,369-372)
                 res.traj_derived = np.zeros((total.value, _lib().rt_traj_derived_columns(self._ctx)))
                 _check(_lib().rt_traj_derived(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj_derived)), self._ctx)
+        return res
+
+
+class MultiRayTracer:
+    """The same solve over several GPUs of one box from ONE process (rt_multi_* / rt_solve_*_multi): one context and one
+    host thread per device, block-cyclic launch-list partition inside the library, results in launch order in the
+    caller's arrays.  devices: list of CUDA device indices (None = all visible)."""
+
+    def __init__(self, preset="lat2d", devices=None, env=None, opts=None, block=0):
+        self._m = C.c_void_p()
+        L = _lib()
+        L.rt_multi_last_error.restype = C.c_char_p
+        L.rt_multi_last_error.argtypes = [C.c_void_p]
+        L.rt_multi_global_index.restype = C.c_int64
+        L.rt_multi_ctx.restype = C.c_void_p
+        n = 0 if devices is None else len(devices)
+        arr = None if devices is None else (C.c_int * n)(*devices)
+        _check(L.rt_multi_create(C.byref(self._m), C.c_int(n), arr))
+        self.ngpu = L.rt_multi_count(self._m)
+        self.preset = _preset_id(preset)
+        self.env = env if env is not None else env_preset(self.preset)
+        self.opts = opts if opts is not None else solver_preset(self.preset)
+        self._mcheck(L.rt_multi_set_env(self._m, C.byref(self.env)))
+        self._mcheck(L.rt_multi_set_solver(self._m, C.byref(self.opts)))
+        if block:
+            self._mcheck(L.rt_multi_set_block(self._m, C.c_int64(block)))
+
+    def _mcheck(self, rc):
+        if rc != 0:
+            raise RuntimeError(f"raytrace_b200 error {rc}: {_lib().rt_multi_last_error(self._m).decode()}")
+
+    def close(self):
+        if self._m:
+            _lib().rt_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def dim(self):
+        return 7 if self.env.preset == 1 else 4
+
+    def set_solver(self, opts=None, **kw):
+        o = opts if opts is not None else self.opts
+        for k, v in kw.items():
+            setattr(o, k, v)
+        self._mcheck(_lib().rt_multi_set_solver(self._m, C.byref(o)))
+        self.opts = o
+
+    def partition(self, n):
+        """(block length, rays per device) of a solve of n rays."""
+        b = C.c_int64()
+        cnt = (C.c_int64 * self.ngpu)()
+        self._mcheck(_lib().rt_multi_partition(self._m, C.c_int64(n), C.byref(b), cnt))
+        return b.value, list(cnt)
+
+    def global_index(self, n, gpu, local):
+        return int(_lib().rt_multi_global_index(self._m, C.c_int64(n), C.c_int(gpu), C.c_int64(local)))
+
+    def stats(self, gpu):
+        s = Stats()
+        self._mcheck(_lib().rt_multi_get_stats(self._m, C.c_int(gpu), C.byref(s)))
+        return s
+
+    def solve(self, launch, res=None):
+        """Trace a launch list [5 or 9, n] (host array; pinned arrays in `res` — a SolveResult — get the early copy)."""
+        launch = np.ascontiguousarray(np.asarray(launch, dtype=np.float64))
+        ncol = 9 if self.dim == 7 else 5
+        if launch.ndim != 2 or launch.shape[0] != ncol:
+            raise ValueError(f"launch list must be [{ncol}, n]")
+        n = launch.shape[1]
+        res = res if res is not None else SolveResult(n, self.dim)
+        cres = res._c()
+        fn = _lib().rt_solve_3d_multi if self.dim == 7 else _lib().rt_solve_2d_multi
+        self._mcheck(fn(self._m, C.c_int64(n), *[_ptr(launch[k]) for k in range(ncol)], C.byref(cres)))
         return res
 
 

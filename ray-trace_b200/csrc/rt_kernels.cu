@@ -20,6 +20,40 @@ static thread_local std::string g_last_error;
 
 #define RT_LATE_CAP 65536  // rays that may still be running when the early result copy starts
 
+// Where a context's rays sit in the caller's HOST arrays.  Single-GPU calls: local ray j is element j.  Multi-GPU calls
+// (rt_solve_*_multi) partition the launch list block-cyclically: blocks of B consecutive rays go round the N devices, so
+// device d's local ray j is element (j / B) (N B) + d B + j % B of the caller's arrays, and every column moves with ONE
+// 2D copy (width B elements, pitch N B elements) straight between the caller's arrays and device memory.
+struct RtHostLayout {
+  long long B;  // block length in rays
+  int N, d;     // devices, this device
+};
+static inline long long rt_to_global(const RtHostLayout *L, long long j) {
+  return L ? (j / L->B) * (L->B * (long long)L->N) + (long long)L->d * L->B + (j % L->B) : j;
+}
+static long long rt_local_count(long long n, long long B, int N, int d) {
+  const long long cycle = B * (long long)N, full = n / cycle, rem = n % cycle - (long long)d * B;
+  return full * B + (rem < 0 ? 0 : (rem > B ? B : rem));
+}
+// one column (n_local elements of esz bytes, local order on the device) <-> the caller's host array (global order)
+static cudaError_t rt_copy_col(const RtHostLayout *L, void *dev, void *host, size_t esz, long long n_local, bool to_host,
+                               cudaStream_t st) {
+  const cudaMemcpyKind kind = to_host ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice;
+  if (n_local <= 0) return cudaSuccess;
+  if (!L) return to_host ? cudaMemcpyAsync(host, dev, (size_t)n_local * esz, kind, st) : cudaMemcpyAsync(dev, host, (size_t)n_local * esz, kind, st);
+  const long long full = n_local / L->B, rem = n_local % L->B;
+  char *h0 = (char *)host + (size_t)L->d * L->B * esz;
+  const size_t w = (size_t)L->B * esz, hp = w * (size_t)L->N;
+  cudaError_t e = cudaSuccess;
+  if (full > 0)
+    e = to_host ? cudaMemcpy2DAsync(h0, hp, dev, w, w, (size_t)full, kind, st) : cudaMemcpy2DAsync(dev, w, h0, hp, w, (size_t)full, kind, st);
+  if (e == cudaSuccess && rem > 0) {
+    char *hh = h0 + (size_t)full * hp, *dd = (char *)dev + (size_t)full * w;
+    e = to_host ? cudaMemcpyAsync(hh, dd, (size_t)rem * esz, kind, st) : cudaMemcpyAsync(dd, hh, (size_t)rem * esz, kind, st);
+  }
+  return e;
+}
+
 struct rt_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;      // stream in use
@@ -45,6 +79,8 @@ struct rt_ctx {
   int *late_idx = nullptr, *late_i = nullptr, *late_hi = nullptr;  // device list, device / pinned packed int records
   double *late_d = nullptr, *late_hd = nullptr;                    // device / pinned packed double records
   const rt_result *early_host = nullptr;                           // non-null during a host-pointer solve with pinned results
+  const RtHostLayout *layout = nullptr;                            // non-null during a multi-GPU solve (block-cyclic host arrays)
+  long long n_global = 0;                                          // length of the caller's host arrays during a host-pointer solve
   bool early_done = false;
   long long late_n = 0;
   double *traj = nullptr;
@@ -707,6 +743,22 @@ __global__ void rt_late_gather_kernel(int m, int dim, long long n, const int *la
   oi[(size_t)4 * m + j] = R.nreflect[i];
 }
 
+// every result array of the (device) record R to the caller's host arrays H, on stream st
+static int copy_results_to_host(rt_ctx *ctx, const rt_result &H, const rt_result &R, long long n, int dim, cudaStream_t st) {
+  const RtHostLayout *Y = ctx->layout;
+  const size_t ng = (size_t)ctx->n_global;
+  for (int c = 0; c < dim; c++)
+    RT_CUDA(ctx, rt_copy_col(Y, R.u_end + (size_t)c * n, H.u_end + (size_t)c * ng, sizeof(double), n, true, st));
+  RT_CUDA(ctx, rt_copy_col(Y, R.t_end, H.t_end, sizeof(double), n, true, st));
+  RT_CUDA(ctx, rt_copy_col(Y, R.group_delay, H.group_delay, sizeof(double), n, true, st));
+  RT_CUDA(ctx, rt_copy_col(Y, R.status, H.status, sizeof(int), n, true, st));
+  RT_CUDA(ctx, rt_copy_col(Y, R.naccept, H.naccept, sizeof(int), n, true, st));
+  RT_CUDA(ctx, rt_copy_col(Y, R.nreject, H.nreject, sizeof(int), n, true, st));
+  RT_CUDA(ctx, rt_copy_col(Y, R.nfe, H.nfe, sizeof(int), n, true, st));
+  RT_CUDA(ctx, rt_copy_col(Y, R.nreflect, H.nreflect, sizeof(int), n, true, st));
+  return RT_OK;
+}
+
 template <int MODE>
 static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_result &R) {
   constexpr int DIM = RtTraits<MODE>::DIM, NCOL = RtTraits<MODE>::NCOL;
@@ -860,19 +912,11 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
           if (++nsnap == 4) {
             cudaStream_t cs = ctx->copy_stream;
             const rt_result &H = *ctx->early_host;
-            const size_t nb = (size_t)n * sizeof(double), ib = (size_t)n * sizeof(int);
             for (int q = 0; q < 4; q++) RT_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_snap[q], 0));
             rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, cs>>>(n, R.u_end + (size_t)(DIM - 1) * n, ctx->par,
                                                                     MODE == RT_PRESET_RAY3D, R.group_delay);
             ctx->stats.kernel_launches++;
-            RT_CUDA(ctx, cudaMemcpyAsync(H.u_end, R.u_end, DIM * nb, cudaMemcpyDeviceToHost, cs));
-            RT_CUDA(ctx, cudaMemcpyAsync(H.t_end, R.t_end, nb, cudaMemcpyDeviceToHost, cs));
-            RT_CUDA(ctx, cudaMemcpyAsync(H.group_delay, R.group_delay, nb, cudaMemcpyDeviceToHost, cs));
-            RT_CUDA(ctx, cudaMemcpyAsync(H.status, R.status, ib, cudaMemcpyDeviceToHost, cs));
-            RT_CUDA(ctx, cudaMemcpyAsync(H.naccept, R.naccept, ib, cudaMemcpyDeviceToHost, cs));
-            RT_CUDA(ctx, cudaMemcpyAsync(H.nreject, R.nreject, ib, cudaMemcpyDeviceToHost, cs));
-            RT_CUDA(ctx, cudaMemcpyAsync(H.nfe, R.nfe, ib, cudaMemcpyDeviceToHost, cs));
-            RT_CUDA(ctx, cudaMemcpyAsync(H.nreflect, R.nreflect, ib, cudaMemcpyDeviceToHost, cs));
+            if (int rc = copy_results_to_host(ctx, H, R, n, DIM, cs)) return rc;
             RT_CUDA(ctx, cudaEventRecord(ctx->ev_copy, cs));
             ctx->early_done = true;
             if (dbg) fprintf(stderr, "[rt] early result copy enqueued, %lld rays still running\n", ctx->late_n);
@@ -980,8 +1024,11 @@ static bool result_ok(const rt_result *r) {
   return r && r->u_end && r->t_end && r->group_delay && r->status && r->naccept && r->nreject && r->nfe && r->nreflect;
 }
 
+// n = this context's rays.  Host-pointer calls: cols / res are the caller's arrays of n_global elements and `layout`
+// says which of them are this context's (null: all, n_global == n).
 static int solve_common(rt_ctx *ctx, int64_t n, const double *const *cols, int ncols, rt_result *res, bool want3d,
-                        bool on_device) {
+                        bool on_device, const RtHostLayout *layout = nullptr, int64_t n_global = -1) {
+  if (n_global < 0) n_global = n;
   if (!ctx) return set_err(ctx, RT_ERR_INVALID, "rt_solve: null context");
   if (n < 0 || n > 2000000000LL) return set_err(ctx, RT_ERR_INVALID, "rt_solve: n out of range");
   if ((ctx->env.preset == RT_PRESET_RAY3D) != want3d)
@@ -998,6 +1045,8 @@ static int solve_common(rt_ctx *ctx, int64_t n, const double *const *cols, int n
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   const int dim = want3d ? 7 : 4;
   RtLaunch L{};
+  ctx->layout = nullptr;
+  ctx->n_global = n;
   if (on_device) {
     for (int k = 0; k < ncols; k++) L.col[k] = cols[k];
     return dispatch_solve(ctx, n, L, *res);
@@ -1006,8 +1055,10 @@ static int solve_common(rt_ctx *ctx, int64_t n, const double *const *cols, int n
   const size_t nb = (size_t)n * sizeof(double);
   if (int rc = ensure_stage(ctx, (size_t)(ncols + dim + 2) * nb, (size_t)5 * n * sizeof(int))) return rc;
   double *d = ctx->stage_d;
+  ctx->layout = layout;
+  ctx->n_global = n_global;
   for (int k = 0; k < ncols; k++) {
-    RT_CUDA(ctx, cudaMemcpyAsync(d + (size_t)k * n, cols[k], nb, cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, rt_copy_col(layout, d + (size_t)k * n, const_cast<double *>(cols[k]), sizeof(double), n, false, ctx->stream));
     L.col[k] = d + (size_t)k * n;
   }
   rt_result D;
@@ -1043,24 +1094,17 @@ static int solve_common(rt_ctx *ctx, int64_t n, const double *const *cols, int n
     std::vector<int> li(m);
     if (m) RT_CUDA(ctx, cudaMemcpy(li.data(), ctx->late_idx, m * sizeof(int), cudaMemcpyDeviceToHost));
     int *ints[5] = {res->status, res->naccept, res->nreject, res->nfe, res->nreflect};
+    const size_t ng = (size_t)n_global;
     for (size_t j = 0; j < m; j++) {
-      const size_t i = (size_t)li[j];
-      for (int c = 0; c < dim; c++) res->u_end[(size_t)c * n + i] = ctx->late_hd[(size_t)c * m + j];
+      const size_t i = (size_t)rt_to_global(layout, li[j]);
+      for (int c = 0; c < dim; c++) res->u_end[c * ng + i] = ctx->late_hd[(size_t)c * m + j];
       res->t_end[i] = ctx->late_hd[(size_t)dim * m + j];
       res->group_delay[i] = ctx->late_hd[(size_t)(dim + 1) * m + j];
       for (int q = 0; q < 5; q++) ints[q][i] = ctx->late_hi[(size_t)q * m + j];
     }
     return RT_OK;
   }
-  RT_CUDA(ctx, cudaMemcpyAsync(res->u_end, D.u_end, dim * nb, cudaMemcpyDeviceToHost, st));
-  RT_CUDA(ctx, cudaMemcpyAsync(res->t_end, D.t_end, nb, cudaMemcpyDeviceToHost, st));
-  RT_CUDA(ctx, cudaMemcpyAsync(res->group_delay, D.group_delay, nb, cudaMemcpyDeviceToHost, st));
-  const size_t ib = (size_t)n * sizeof(int);
-  RT_CUDA(ctx, cudaMemcpyAsync(res->status, D.status, ib, cudaMemcpyDeviceToHost, st));
-  RT_CUDA(ctx, cudaMemcpyAsync(res->naccept, D.naccept, ib, cudaMemcpyDeviceToHost, st));
-  RT_CUDA(ctx, cudaMemcpyAsync(res->nreject, D.nreject, ib, cudaMemcpyDeviceToHost, st));
-  RT_CUDA(ctx, cudaMemcpyAsync(res->nfe, D.nfe, ib, cudaMemcpyDeviceToHost, st));
-  RT_CUDA(ctx, cudaMemcpyAsync(res->nreflect, D.nreflect, ib, cudaMemcpyDeviceToHost, st));
+  if (int rc = copy_results_to_host(ctx, *res, D, n, dim, st)) return rc;
   RT_CUDA(ctx, cudaStreamSynchronize(st));
   return RT_OK;
 }
@@ -1086,6 +1130,140 @@ extern "C" int rt_solve_3d_device(rt_ctx *ctx, int64_t n, const double *r, const
                                   const double *T0, const double *f, const double *t0, rt_result *res) {
   const double *cols[9] = {r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0};
   return solve_common(ctx, n, cols, 9, res, true, true);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Multi-GPU behind the boundary: one process, one context and one host thread per device, the launch
+// list partitioned block-cyclically inside the library, terminal records delivered straight into the caller's arrays.
+// Rays are independent (RayTrace_3D.jl:327-359 shares nothing between rays): no device-to-device exchange at all.
+// ---------------------------------------------------------------------------------------------------
+struct rt_multi {
+  std::vector<rt_ctx *> ctx;
+  std::vector<RtHostLayout> lay;
+  std::vector<long long> nloc;
+  std::string err;
+  long long block = 0;  // 0 = automatic
+};
+
+extern "C" int rt_multi_create(rt_multi **out, int ngpu, const int *devices) {
+  if (!out) return set_err(nullptr, RT_ERR_INVALID, "rt_multi_create: null output pointer");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return set_err(nullptr, RT_ERR_NO_DEVICE, "rt_multi_create: no CUDA device available (%s); this library has no CPU fallback",
+                   e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (ngpu <= 0) ngpu = ndev;
+  if (ngpu > ndev && !devices) return set_err(nullptr, RT_ERR_INVALID, "rt_multi_create: %d devices asked, %d visible", ngpu, ndev);
+  rt_multi *m = new rt_multi();
+  for (int k = 0; k < ngpu; k++) {
+    rt_ctx *c = nullptr;
+    const int rc = rt_create(&c, devices ? devices[k] : k);  // (the same device may be listed twice: tests on one GPU)
+    if (rc != RT_OK) {
+      for (rt_ctx *q : m->ctx) rt_destroy(q);
+      delete m;
+      return rc;
+    }
+    m->ctx.push_back(c);
+  }
+  m->lay.resize(ngpu);
+  m->nloc.resize(ngpu);
+  *out = m;
+  return RT_OK;
+}
+
+extern "C" void rt_multi_destroy(rt_multi *m) {
+  if (!m) return;
+  for (rt_ctx *c : m->ctx) rt_destroy(c);
+  delete m;
+}
+
+extern "C" int rt_multi_count(const rt_multi *m) { return m ? (int)m->ctx.size() : RT_ERR_INVALID; }
+extern "C" rt_ctx *rt_multi_ctx(rt_multi *m, int k) { return (m && k >= 0 && k < (int)m->ctx.size()) ? m->ctx[k] : nullptr; }
+extern "C" const char *rt_multi_last_error(const rt_multi *m) { return m ? m->err.c_str() : g_last_error.c_str(); }
+
+extern "C" int rt_multi_set_env(rt_multi *m, const rt_env_params *env) {
+  if (!m) return set_err(nullptr, RT_ERR_INVALID, "rt_multi_set_env: null context");
+  for (rt_ctx *c : m->ctx)
+    if (int rc = rt_set_env(c, env)) { m->err = c->err; return rc; }
+  return RT_OK;
+}
+extern "C" int rt_multi_set_solver(rt_multi *m, const rt_solver_opts *o) {
+  if (!m) return set_err(nullptr, RT_ERR_INVALID, "rt_multi_set_solver: null context");
+  for (rt_ctx *c : m->ctx)
+    if (int rc = rt_set_solver(c, o)) { m->err = c->err; return rc; }
+  return RT_OK;
+}
+extern "C" int rt_multi_set_block(rt_multi *m, int64_t block) {
+  if (!m || block < 0) return set_err(nullptr, RT_ERR_INVALID, "rt_multi_set_block: bad argument");
+  m->block = block;
+  return RT_OK;
+}
+
+// the partition the next solve of n rays would use: block length, and per device the local count
+static long long multi_block(const rt_multi *m, long long n) {
+  if (m->block > 0) return m->block;
+  // rows of 32 kB keep the 2D copies at PCIe speed; small enough that every device sees >= 32 blocks spread over the
+  // whole launch list (the expensive rays of a sweep cluster in launch-parameter space: on the 8 x 10^6-ray cfg3 sweep
+  // 4096-ray blocks leave the devices' work within 0.5 % of each other, 16384-ray blocks within 1 %)
+  const long long N = (long long)m->ctx.size();
+  long long B = 4096;
+  while (B > 128 && n / (B * N) < 32) B /= 2;
+  return B;
+}
+extern "C" int rt_multi_partition(rt_multi *m, int64_t n, int64_t *block, int64_t *counts) {
+  if (!m || n < 0) return set_err(nullptr, RT_ERR_INVALID, "rt_multi_partition: bad argument");
+  const long long B = multi_block(m, n);
+  if (block) *block = B;
+  if (counts)
+    for (int d = 0; d < (int)m->ctx.size(); d++) counts[d] = rt_local_count(n, B, (int)m->ctx.size(), d);
+  return RT_OK;
+}
+extern "C" int64_t rt_multi_global_index(rt_multi *m, int64_t n, int gpu, int64_t local) {
+  if (!m || gpu < 0 || gpu >= (int)m->ctx.size()) return -1;
+  RtHostLayout L{multi_block(m, n), (int)m->ctx.size(), gpu};
+  return rt_to_global(&L, local);
+}
+
+static int solve_multi(rt_multi *m, int64_t n, const double *const *cols, int ncols, rt_result *res, bool want3d) {
+  if (!m) return set_err(nullptr, RT_ERR_INVALID, "rt_solve_multi: null context");
+  const int N = (int)m->ctx.size();
+  if (n < 0) { m->err = "rt_solve_multi: n out of range"; return RT_ERR_INVALID; }
+  if (n > 0 && !result_ok(res)) { m->err = "rt_solve_multi: rt_result has null members"; return RT_ERR_INVALID; }
+  const long long B = multi_block(m, n);
+  std::vector<int> rc(N, RT_OK);
+  std::vector<std::thread> th;
+  for (int d = 0; d < N; d++) {
+    m->lay[d] = RtHostLayout{B, N, d};
+    m->nloc[d] = rt_local_count(n, B, N, d);
+    th.emplace_back([=, &rc]() {
+      rc[d] = solve_common(m->ctx[d], m->nloc[d], cols, ncols, res, want3d, false, &m->lay[d], n);
+    });
+  }
+  for (auto &t : th) t.join();
+  for (int d = 0; d < N; d++)
+    if (rc[d] != RT_OK) {
+      m->err = "device " + std::to_string(d) + ": " + m->ctx[d]->err;
+      g_last_error = m->err;
+      return rc[d];
+    }
+  return RT_OK;
+}
+
+extern "C" int rt_solve_2d_multi(rt_multi *m, int64_t n, const double *r, const double *theta, const double *chi,
+                                 const double *f, const double *t0, rt_result *res) {
+  const double *cols[5] = {r, theta, chi, f, t0};
+  return solve_multi(m, n, cols, 5, res, false);
+}
+extern "C" int rt_solve_3d_multi(rt_multi *m, int64_t n, const double *r, const double *theta, const double *phi,
+                                 const double *rho_r, const double *rho_theta, const double *rho_phi, const double *T0,
+                                 const double *f, const double *t0, rt_result *res) {
+  const double *cols[9] = {r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0};
+  return solve_multi(m, n, cols, 9, res, true);
+}
+extern "C" int rt_multi_get_stats(const rt_multi *m, int gpu, rt_stats *st) {
+  if (!m || gpu < 0 || gpu >= (int)m->ctx.size()) return set_err(nullptr, RT_ERR_INVALID, "rt_multi_get_stats: bad argument");
+  return rt_get_stats(m->ctx[gpu], st);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -66,6 +66,15 @@ def partition_indices(n, rank, world, layout="contiguous"):
     return _np.arange(lo, hi)
 
 
+def block_cyclic_indices(n, block, world, rank):
+    """Launch-list indices of device `rank` under the library's multi-GPU partition (rt_solve_*_multi): blocks of
+    `block` consecutive rays go round the `world` devices; local ray j is element (j // block) * block * world +
+    rank * block + j % block."""
+    import numpy as _np
+    idx = _np.arange(n, dtype=_np.int64)
+    return idx[(idx // block) % world == rank]
+
+
 def launch_angle(b, hbi=1.0e6, re=RE):
     """Wave-normal launch angle helper of scratch.jl:725-731: for a ray leaving the ground at angle b from the
     vertical, alpha = acos((re sin^2 b + cos b sqrt((re+hbi)^2 - re^2 sin^2 b)) / (re+hbi)) is the geocentric angle

@@ -110,3 +110,21 @@ def test_launch_angle_helper_reproduces_the_scratch_cell():
     alpha = math.acos((re * math.sin(b) ** 2.0 + math.cos(b) * ((re + hbi) ** 2.0 - re ** 2.0 * math.sin(b) ** 2.0) ** 0.5) / (re + hbi))
     a, chi = sweeps.launch_angle(b)
     assert abs(a - alpha) < 1e-15 and abs(chi - (b - alpha)) < 1e-15 and 0 < a < 0.3
+
+
+def test_block_cyclic_partition_mirror_and_multi_create_without_gpu(have_gpu):
+    """The multi-GPU partition of rt_solve_*_multi (blocks of B rays go round the devices), as sweeps mirrors it; and
+    rt_multi_create fails loudly without a device like rt_create does."""
+    from raytrace_b200 import sweeps
+    for n, B, N in ((1000, 128, 3), (5, 2, 2), (0, 4, 2), (16384 * 8 + 5, 16384, 8)):
+        parts = [sweeps.block_cyclic_indices(n, B, N, r) for r in range(N)]
+        assert sorted(np.concatenate(parts).tolist()) == list(range(n))
+        for r, p in enumerate(parts):
+            j = np.arange(p.size)
+            assert np.array_equal(p, (j // B) * (B * N) + r * B + j % B)
+    if not have_gpu:
+        m = C.c_void_p()
+        lib = C.CDLL(R.lib_path())
+        assert lib.rt_multi_create(C.byref(m), C.c_int(2), None) == -2 and not m.value  # RT_ERR_NO_DEVICE
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            R.MultiRayTracer("ray3d", devices=[0, 1])

@@ -506,3 +506,43 @@ def test_plasmasphere_jl_batch_bitexact():
     with pytest.raises(RuntimeError, match="RAY3D"):
         rt3.plasmasphere(r[:4], lam[:4])
     rt3.close()
+
+
+def test_multi_gpu_entry_point_block_cyclic_partition():
+    """rt_solve_*_multi: one process, one context + host thread per device, block-cyclic partition inside the library,
+    records in launch order in the caller's arrays.  Two contexts on device 0 stand in for two GPUs (rays are
+    independent, so the result must equal the single-context solve bit for bit); ragged sizes, pinned and pageable."""
+    import torch
+    full = sweeps.sweep_3d(12, 3, 24)
+    rt = R.RayTracer("ray3d")
+    rt.set_solver(maxiters=600, r_esc=10 * RE)
+    one = rt.solve(full)
+    rt.close()
+    ndev = torch.cuda.device_count()
+    for devices, block in (([0, 0], 128), ([0, 0, 0], 200), ([0], 0), (list(range(min(ndev, 8))), 0)):
+        m = R.MultiRayTracer("ray3d", devices=devices, block=block)
+        m.set_solver(maxiters=600, r_esc=10 * RE)
+        for n in (full.shape[1], 777, 1, 0):
+            res = R.api.SolveResult(n, 7)
+            if n == 777:  # pinned result arrays: the early-copy path of every device
+                for name in ("u_end", "t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
+                    setattr(res, name, torch.from_numpy(getattr(res, name)).pin_memory().numpy())
+            m.solve(np.ascontiguousarray(full[:, :n]), res)
+            for k in ("t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
+                assert _same(getattr(res, k), getattr(one, k)[:n]), (devices, n, k)
+            assert _same(res.u_end, one.u_end[:, :n])
+            b, counts = m.partition(n)
+            assert sum(counts) == n and b >= 1
+            for g in range(len(devices)):
+                idx = sweeps.block_cyclic_indices(n, b, len(devices), g)
+                assert idx.size == counts[g]
+                if idx.size:
+                    assert m.global_index(n, g, idx.size - 1) == idx[-1] and m.global_index(n, g, 0) == idx[0]
+        assert m.stats(0).kernel_launches >= 0
+        m.close()
+    m2 = R.MultiRayTracer("lat2d", devices=[0, 0], block=16)
+    m2.set_solver(maxiters=150)
+    launch = sweeps.sweep_2d(7, 19)
+    res = m2.solve(launch)
+    m2.close()
+    _check_solve(res, O.solve_batch(O.env(O.LAT2D), O.opts(maxiters=150), launch, False, 4), 1e-10)

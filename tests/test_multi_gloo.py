@@ -31,12 +31,13 @@ def _worker(rank, world, port, out_path, n_total, layout):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     full = sweeps.sweep_3d(3, 7, 5)[:, :n_total]
-    part = np.ascontiguousarray(full[:, sweeps.partition_indices(n_total, rank, world, layout)])
+    part = np.ascontiguousarray(full[:, multi._indices(n_total, rank, world, layout)])
     res = O.solve_batch(O.env(O.RAY3D), O.opts(reltol=1e-3, dtmax=0, dtmin=0, r_esc=10 * sweeps.RE), part, True, 1)
     T = torch.from_numpy
     d, i = multi.pack_terminal(T(res["u_end"]), T(res["t_end"]), T(res["u_end"][6].copy()), T(res["status"]),
                                T(res["naccept"]), T(res["nreject"]), T(res["nfe"]), T(res["nreflect"]))
     D, I = multi.gather_terminal(d, i, n_total, rank, world, layout=layout)
+    D, I = multi.gather_terminal(d, i, n_total, rank, world, layout=layout)  # a second step reuses the plan's buffers
     if rank == 0:
         np.savez(out_path, D=D.numpy(), I=I.numpy())
     else:
@@ -48,7 +49,7 @@ def _worker(rank, world, port, out_path, n_total, layout):
 import pytest
 
 
-@pytest.mark.parametrize("layout", ["contiguous", "strided", "rotated"])
+@pytest.mark.parametrize("layout", ["contiguous", "strided", "rotated", "blockcyclic:8"])
 def test_two_rank_partition_and_gather(tmp_path, layout):
     from raytrace_b200 import sweeps
     n_total = 101  # odd: ragged partitions 50 + 51
