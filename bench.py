@@ -35,16 +35,19 @@ RE = 6.3712e6
 # Algorithmic FP64 work per Haselgrove RHS evaluation: executed
 # DADD + DMUL + 2*DFMA per RHS of the minimal faithful schedule, calibrated once with ncu
 # (profiles/r1_flop_calibration.md) and frozen.
-FLOP_PER_RHS = {"cfg3": 2602.0, "cfg5": 2602.0, "cfg2": 2307.0, "cfg4": 2307.0}
-IS3D = {"cfg3": True, "cfg5": True, "cfg2": False, "cfg4": False}
-SCALING = {"cfg3": "weak", "cfg2": "weak", "cfg4": "weak", "cfg5": "strong"}
+FLOP_PER_RHS = {"cfg3": 2602.0, "cfg5": 2602.0, "cfg2": 2307.0, "cfg4": 2307.0, "cfg2save": 2307.0}
+IS3D = {"cfg3": True, "cfg5": True, "cfg2": False, "cfg4": False, "cfg2save": False}
+SCALING = {"cfg3": "weak", "cfg2": "weak", "cfg4": "weak", "cfg5": "strong", "cfg2save": "weak"}
+# "cfg2save": the cfg2 launch list with the reference's save-every-step output on (RayTrace_lat.jl:318-329,345-372):
+# 8192 rows of 72 B per ray, iteration cap 8190 so that no trajectory is truncated -> 59 GB of trajectory rows per step
+SAVE_ROWS = 8192
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-list launch of rt_integrate_kernel (4 attempts for each of
 # 10^6 rays, 7813 blocks) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v3.md:
 # 176.3 MB + 115.6 MB.  Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 10^6 = 0.4 GB upper bound.
 # launch-list partition across ranks: block b of N consecutive rays goes to the ranks rotated by b, so that every GPU
 # gets its share of the long rays AND of every wave-normal angle (plain strided: +-4.5 % work per rank on 8 GPUs)
 PARTITION = "rotated"
-NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 291.9e6, "cfg5": None, "cfg2": 13.3e6, "cfg4": None}
+NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 291.9e6, "cfg5": None, "cfg2": 13.3e6, "cfg4": None, "cfg2save": None}
 
 
 def parse():
@@ -52,7 +55,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg2", "cfg4", "cfg5"])
+    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg2", "cfg4", "cfg5", "cfg2save"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays-per-gpu", type=int, default=0, help="override (testing only)")
     ap.add_argument("--slice", type=int, default=0)
@@ -97,6 +100,8 @@ def solver_kwargs(workload, slice_attempts=0):
         kw = dict(adaptive=1, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, maxiters=1000000, t1=5.0e10, r_esc=10 * RE)
     else:  # RayTrace_lat.jl:338
         kw = dict(adaptive=1, reltol=1e-7, abstol=1e-6, dtmax=1e6, dtmin=1e-8, maxiters=100000, t1=5.0e9, r_esc=10 * RE)
+    if workload == "cfg2save":
+        kw.update(maxiters=SAVE_ROWS - 2, save_mode=1, max_samples=SAVE_ROWS, save_stride=1)
     if MAXITERS_OVERRIDE:
         kw["maxiters"] = MAXITERS_OVERRIDE
     if slice_attempts:
@@ -180,7 +185,7 @@ def cpu_sample(workload, launch, nrays):
     return np.ascontiguousarray(launch[:, idx])
 
 
-CPU_SAMPLE_DEFAULT = {"cfg3": 40000, "cfg5": 40000, "cfg2": 96, "cfg4": 32}
+CPU_SAMPLE_DEFAULT = {"cfg3": 40000, "cfg5": 40000, "cfg2": 96, "cfg4": 32, "cfg2save": 256}
 
 
 def run_reference(args, rank, world):
@@ -295,6 +300,43 @@ def main():
     dev_res = {"u_end": u_end.cpu().numpy(), "t_end": t_end.cpu().numpy(), "group_delay": gd.cpu().numpy(),
                "status": status_h, "naccept": ints[1].cpu().numpy(), "nreject": ints[2].cpu().numpy(),
                "nfe": ints[3].cpu().numpy(), "nreflect": ints[4].cpu().numpy()}
+    # trajectory output (save workloads): rows written per step, the same sweep without saving, and the CSR packing
+    traj = None
+    if rank == 0 and solver_kwargs(args.workload).get("save_mode"):
+        lib = R.api._lib()
+        total = ctypes.c_int64()
+        if lib.rt_traj_size(rt._ctx, ctypes.byref(total)) != 0:
+            raise RuntimeError(lib.rt_last_error(rt._ctx).decode())
+        ncol_t = lib.rt_traj_columns(rt._ctx)
+        tbytes = total.value * ncol_t * 8
+        flags = np.zeros(n, np.int32)
+        lib.rt_traj_truncated(rt._ctx, flags.ctypes.data_as(ctypes.c_void_p))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        d_off, d_rows, tot2 = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_int64()
+        pack_ms = []
+        for _ in range(3):
+            e0.record(stream)
+            if lib.rt_traj_pack_device(rt._ctx, ctypes.byref(d_off), ctypes.byref(d_rows), ctypes.byref(tot2)) != 0:
+                raise RuntimeError(lib.rt_last_error(rt._ctx).decode())
+            e1.record(stream)
+            torch.cuda.synchronize()
+            pack_ms.append(e0.elapsed_time(e1))
+        kw0 = dict(solver_kwargs(args.workload, args.slice), save_mode=0, max_samples=0)
+        rt.set_solver(**kw0)
+        rt.solve_device(n, cols, res_ptrs)
+        st0 = rt.solve_device(n, cols, res_ptrs)
+        rt.set_solver(**solver_kwargs(args.workload, args.slice))
+        step_ms = ms_local / args.steps
+        traj = {"rows_per_step": int(total.value), "bytes_per_step": int(tbytes), "row_bytes": ncol_t * 8,
+                "truncated_rays": int(flags.sum()),
+                "write_gbs_over_the_step": tbytes / (step_ms * 1e-3) / 1e9,
+                "step_ms_saving": step_ms, "step_ms_not_saving": st0.total_ms,
+                "pack_ms": min(pack_ms), "pack_gbs": 2 * tbytes / (min(pack_ms) * 1e-3) / 1e9,
+                "pack_note": "rt_traj_pack_device: cub scan of the row counts + one coalesced copy kernel; "
+                             "bytes read + written over its time, against hbm_gbs of MEASURED_PEAKS.json",
+                "hbm_gbs_measured": json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs")
+                if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else None}
+
     # diagnostic, outside the timed region: the integrate kernel in steady state (every ray alive, full lists):
     # the same sweep cut off after 24 step attempts, one chain
     steady = None
@@ -403,6 +445,7 @@ def main():
             "e2e": {"value": nfe_all * K / (e2e_all * 1e-3), "unit": "RHS evals/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_all / K,
                     "rays_per_s": rays_all * K / (e2e_all * 1e-3)},
+            "trajectory": traj,
             "gpu_launches": int(launches_all),
             "by_rank": by_rank,
             "clocks": clocks,

@@ -79,7 +79,7 @@ typedef struct rt_env_params {
 typedef struct rt_solver_opts {
   int32_t adaptive;      /* 1 = Tsit5 + PI controller; 0 = Tsit5(), adaptive=false, dt=dt */
   int32_t save_mode;     /* 0 = terminal state only; 1 = every accepted step (sol.t / sol[i,:]) */
-  int32_t max_samples;   /* per-ray sample capacity when save_mode = 1 (later samples dropped) */
+  int32_t max_samples;   /* per-ray row capacity when save_mode = 1 (>= 2; see rt_traj_truncated) */
   int32_t save_stride;   /* keep every save_stride-th accepted step (>= 1); end point always kept */
   int64_t maxiters;      /* step attempts (accepted + rejected); SciML default 100000 */
   double t1;             /* tspan[2]; tspan[1] comes per ray from the launch list */
@@ -216,8 +216,15 @@ RT_API int rt_multi_get_stats(const rt_multi *m, int gpu, rt_stats *stats);
  *          3D  t, r, th, ph, rho_r, rho_th, rho_ph, T      (RayTrace_3D.jl:333)             = 8 */
 RT_API int rt_traj_columns(const rt_ctx *ctx);
 RT_API int rt_traj_size(rt_ctx *ctx, int64_t *total_samples);
+/* flags[n]: 1 where a trajectory did not fit max_samples.  Rows 0 .. max_samples-2 take the start and every
+ * save_stride-th accepted step; the last row is reserved for the final sample (event point / tspan end / escape),
+ * so a trajectory that does not fit loses samples before its end, never the end itself */
+RT_API int rt_traj_truncated(rt_ctx *ctx, int32_t *flags);
 /* offsets[n+1] (CSR), samples[total][columns] row-major */
 RT_API int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples);
+/* the same packed rows and offsets left in DEVICE memory (owned by the context, valid until its next solve or
+ * trajectory call): for consumers that stay on the GPU */
+RT_API int rt_traj_pack_device(rt_ctx *ctx, const int64_t **d_offsets, const double **d_samples, int64_t *total_samples);
 /* what the reference derives from a trajectory after the solve, computed on the device and packed with the same
  * offsets (as returned by rt_traj_copy): 2D  x, y, dt  with x = r cos(lam), y = r sin(lam) (RayTrace_lat.jl:351-352;
  * colatitude presets x = r sin(th), y = r cos(th): RayMain.jl:400-401, scratch.jl:407-408) and

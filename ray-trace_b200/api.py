@@ -137,6 +137,7 @@ class SolveResult:
         self.traj_offsets = None
         self.traj = None
         self.traj_derived = None
+        self.truncated = None  # [n] int32, 1 where a trajectory did not fit max_samples (rt_traj_truncated)
         self.stats = None
 
     def _c(self):
@@ -292,6 +293,8 @@ class RayTracer:
             res.traj_offsets = np.zeros(n + 1, np.int64)
             res.traj = np.zeros((total.value, ncolt))
             _check(_lib().rt_traj_copy(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj)), self._ctx)
+            res.truncated = np.zeros(n, np.int32)
+            _check(_lib().rt_traj_truncated(self._ctx, _ptr(res.truncated)), self._ctx)
             if derived:  # Cartesian track and step sizes, computed on the device (RayTrace_lat.jl:351-352,369-372)
                 res.traj_derived = np.zeros((total.value, _lib().rt_traj_derived_columns(self._ctx)))
                 _check(_lib().rt_traj_derived(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj_derived)), self._ctx)
@@ -426,7 +429,9 @@ class ODESolution:
             self.t = tr[:, 0].copy()
             self.u = tr[:, 1:1 + dim].copy()
             self.saved_mu = tr[:, 1 + dim:].copy()  # saveμ_cb: [mu, dmudpsi, dip, psi] (2D only)
+            self.truncated = bool(res.truncated[k])  # samples were dropped before the final one (max_samples)
         else:
+            self.truncated = False
             self.t, self.u, self.saved_mu = np.array([self.t_end]), self.u_end[None, :], None
 
     def __getitem__(self, key):
@@ -435,12 +440,15 @@ class ODESolution:
 
 
 def solve(prob, alg=None, reltol=None, abstol=None, dtmax=None, dtmin=None, maxiters=None, adaptive=True, dt=None,
-          callback=True, save_everystep=True, max_samples=4096, device=0, r_esc=None, tracer=None):
+          callback=True, save_everystep=True, max_samples=None, device=0, r_esc=None, tracer=None):
     """solve(prob, Tsit5(); reltol, abstol, dtmax, dtmin, maxiters, adaptive, dt, callback) -> ODESolution(s).
 
     Defaults follow SciML (reltol 1e-3, abstol 1e-6, maxiters 1e5) as at RayTrace_3D.jl:395; pass reltol=1e-7,
     dtmax=1e6, dtmin=1e-8 for the RayTrace_lat.jl:338 call.  `callback=True` is the reference's re_cb (terminate
-    at Earth's surface), which is always on in the kernel; callback=False is not supported."""
+    at Earth's surface), which is always on in the kernel; callback=False is not supported.
+    max_samples (rows kept per ray when save_everystep): default maxiters + 2, i.e. nothing can be dropped, as long as
+    all trajectories fit 8 GB of device memory, else as many rows as do; sol.truncated tells when rows were dropped
+    (the final sample is always kept)."""
     if alg is not None and not isinstance(alg, Tsit5):
         raise TypeError("only Tsit5() is implemented (north_star replaces CVODE_BDF by Tsit5)")
     if not callback:
@@ -457,13 +465,16 @@ def solve(prob, alg=None, reltol=None, abstol=None, dtmax=None, dtmin=None, maxi
     o.dt = 0.0 if dt is None else dt
     o.t1 = prob.tspan[1]
     o.r_esc = 0.0 if r_esc is None else r_esc
-    o.save_mode = 1 if save_everystep else 0
-    o.max_samples = max_samples if save_everystep else 0
-    rt.set_solver(o)
     u0 = prob.u0
     single = u0.ndim == 1
     u0 = u0.reshape(rt.dim, -1)
     n = u0.shape[1]
+    if max_samples is None:
+        row_bytes = 8 * (8 if rt.dim == 7 else 9)
+        max_samples = int(max(2, min(o.maxiters + 2, (8 << 30) // (row_bytes * max(n, 1)))))
+    o.save_mode = 1 if save_everystep else 0
+    o.max_samples = max_samples if save_everystep else 0
+    rt.set_solver(o)
     t0 = np.full(n, prob.tspan[0])
     if rt.dim == 7:
         f = _f64(prob.p[0], n)

@@ -46,6 +46,7 @@ struct RtState {
   int *status, *naccept, *nreject, *nfe, *nreflect;  // [n] (caller's result arrays)
   int *sgn;         // [n] sign of d(latitude)/dt at the last accepted step
   int *nsamp;       // [n] trajectory samples written
+  int *trunc;       // [n] 1 when a sample was dropped because max_samples was reached
   double *traj;     // [n][max_samples][NCOL]
 };
 
@@ -173,15 +174,23 @@ __device__ __forceinline__ void rt_rhs(const RtDevEnv &E, const double *y, doubl
   }
 }
 
-// one trajectory row: (t, u[0..DIM)) and, in 2D, the save_func columns (RayTrace_lat.jl:318-324)
+// ---- trajectory output (sol.t / sol[i,:] / saved_mu: RayTrace_lat.jl:318-329,345-372) --------------------------------
+// A ray's samples are rows (t, u[0..DIM)[, mu, dmudpsi, dip, psi]) of its own region traj[ray][max_samples][NCOL], so
+// consecutive samples of one ray are consecutive in memory.  The kernel does not store a row when it is produced (32
+// lanes x NCOL scattered 8-byte stores, one sector each): every thread stages up to RT_STAGE rows in shared memory and
+// the WARP writes a full stage out together, one lane's rows at a time: RT_STAGE * NCOL consecutive doubles per store
+// instruction (144 B in 2D, 128 B in 3D).  Capacity: rows 0 .. max_samples-2 take the regular samples (t0 and every
+// save_stride-th accepted step); the last row is reserved for the final sample (the event point, the step that
+// reaches t1 or escapes), so a trajectory that does not fit is cut in the middle, never at its end, and is flagged
+// in trunc[] (rt_traj_truncated).
+#ifndef RT_STAGE
+#define RT_STAGE 2
+#endif
+
+// one row, straight to global memory (rt_init_kernel's sample 0)
 template <int MODE>
-__device__ __forceinline__ void rt_traj_push(const RtState &S, const RtDevOpts &O, long long i, int &cnt, double t,
-                                             const double *u, const RtExtras2D &ex, bool writer = true) {
-  constexpr int DIM = RtTraits<MODE>::DIM, NCOL = RtTraits<MODE>::NCOL;
-  if (cnt >= O.max_samples) return;
-  cnt++;
-  if (!writer) return;
-  double *row = S.traj + ((size_t)i * (size_t)O.max_samples + (size_t)(cnt - 1)) * NCOL;
+__device__ __forceinline__ void rt_traj_row(double *row, double t, const double *u, const RtExtras2D &ex) {
+  constexpr int DIM = RtTraits<MODE>::DIM;
   row[0] = t;
 #pragma unroll
   for (int c = 0; c < DIM; c++) row[1 + c] = u[c];
@@ -190,6 +199,47 @@ __device__ __forceinline__ void rt_traj_push(const RtState &S, const RtDevOpts &
     row[6] = ex.dmudpsi;
     row[7] = ex.dip;
     row[8] = ex.psi;
+  }
+}
+
+// stage one sample in this thread's shared-memory slot (cnt rows are in global memory, staged in the slot)
+template <int MODE>
+__device__ __forceinline__ void rt_traj_push(const RtDevOpts &O, double *slot, int cnt, int &staged, bool &truncated,
+                                             bool final_sample, double t, const double *u, const RtExtras2D &ex,
+                                             bool writer) {
+  constexpr int NCOL = RtTraits<MODE>::NCOL;
+  if (!final_sample && cnt + staged >= O.max_samples - 1) {
+    truncated = true;
+    return;
+  }
+  if (writer) rt_traj_row<MODE>(slot + staged * NCOL, t, u, ex);
+  staged++;
+}
+
+// warp-cooperative flush: every lane with `want` set gets its staged rows written by the whole warp as one contiguous
+// burst.  Must be reached by all 32 lanes.  `stage_warp` = the shared-memory slots of this warp's 32 threads.
+template <int MODE>
+__device__ __forceinline__ void rt_traj_flush(const RtState &S, const RtDevOpts &O, const double *stage_warp, int i,
+                                              int &cnt, int &staged, bool want, bool writer) {
+  constexpr int NCOL = RtTraits<MODE>::NCOL;
+  const int lane = threadIdx.x & 31;
+  const bool mine = want && staged > 0;
+  unsigned m = __ballot_sync(0xffffffffu, mine && writer);
+  __syncwarp();  // the owners' staging stores are visible to the warp
+  while (m) {
+    const int L = __ffs(m) - 1;
+    m &= m - 1;
+    const int iL = __shfl_sync(0xffffffffu, i, L);
+    const int cL = __shfl_sync(0xffffffffu, cnt, L);
+    const int nL = __shfl_sync(0xffffffffu, staged, L) * NCOL;
+    const double *src = stage_warp + L * (RT_STAGE * NCOL);
+    double *dst = S.traj + ((size_t)iL * (size_t)O.max_samples + (size_t)cL) * NCOL;
+    for (int e = lane; e < nL; e += 32) dst[e] = src[e];
+  }
+  __syncwarp();  // the slots may be overwritten from here on
+  if (mine) {
+    cnt += staged;
+    staged = 0;
   }
 }
 
@@ -336,7 +386,12 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(const __grid_constant
     S.nreflect[i] = 0;
     S.sgn[i] = rt_sign(k1[1]);
     int cnt = 0;
-    if (O.save_mode) rt_traj_push<MODE>(S, O, i, cnt, t0, u, ex);
+    if (O.save_mode) {
+      const bool room = O.max_samples >= 2;  // row 0 is a regular sample; the last row is reserved for the final one
+      if (room) rt_traj_row<MODE>(S.traj + (size_t)i * (size_t)O.max_samples * RtTraits<MODE>::NCOL, t0, u, ex);
+      cnt = room ? 1 : 0;
+      S.trunc[i] = room ? 0 : 1;
+    }
     S.nsamp[i] = cnt;
     running = (status == RT_RUNNING);
     prio = (idx_prio != nullptr) && (k1[0] > 0.0);
@@ -346,7 +401,7 @@ __global__ void __launch_bounds__(RT_BLOCK) rt_init_kernel(const __grid_constant
 }
 
 // ---- the slice kernel -----------------------------------------------------------------------------
-template <int MODE, bool COOP>
+template <int MODE, bool COOP, bool SAVE>
 __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLOCKS)  // COOP runs a few warps per SM: no register cap
     rt_integrate_kernel(const __grid_constant__ RtDevEnv E, RtDevOpts O, RtState S, const int *__restrict__ idx_in,
                         const int *__restrict__ count_in, int *idx_out, int *count_out, int *count_clear,
@@ -393,10 +448,17 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
   }
   bool running = valid && status == RT_RUNNING, hit = false;
   double hit_hi = 1.0;  // upper end of the event bracket in Theta
+  // trajectory staging (save_mode): RT_STAGE rows per thread behind the stage derivatives in shared memory
+  constexpr int NCOL = RtTraits<MODE>::NCOL;
+  double *const stage_warp = rt_smem + 7 * DIM * RT_BLOCK + (threadIdx.x & ~31) * (RT_STAGE * NCOL);
+  double *const slot = stage_warp + lane * (RT_STAGE * NCOL);
+  int staged = 0;
+  bool truncated = false;
   RtExtras2D ex = {0, 0, 0, 0};
 
   for (int a = 0; a < attempts; a++) {
     if (!__any_sync(0xffffffffu, running)) break;
+    if (SAVE) rt_traj_flush<MODE>(S, O, stage_warp, (int)i, cnt, staged, staged == RT_STAGE, writer);
     if (!running) continue;
     if (t >= O.t1) { status = RT_SUCCESS; running = false; continue; }
     if (naccept + nreject >= O.maxiters) { status = RT_MAX_ITERS; running = false; continue; }
@@ -548,14 +610,15 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
     if (sgn != 0 && sgn_prev != 0 && sgn != sgn_prev) nreflect++;
     if (sgn != 0) sgn_prev = sgn;
     const bool escaped = (O.r_esc > 0.0 && u[0] > O.r_esc);
-    if (O.save_mode) {
+    if (SAVE) {
       bool last = (t >= O.t1) || escaped;
-      if ((naccept % O.save_stride) == 0 || last) rt_traj_push<MODE>(S, O, i, cnt, t, u, ex, writer);
+      if ((naccept % O.save_stride) == 0 || last) rt_traj_push<MODE>(O, slot, cnt, staged, truncated, last, t, u, ex, writer);
     }
     if (escaped) { status = RT_ESCAPED; running = false; continue; }
     h = hnew;
   }
 
+  if (SAVE) rt_traj_flush<MODE>(S, O, stage_warp, (int)i, cnt, staged, staged == RT_STAGE, writer);  // room for the event row
   if (hit) {  // re_cb's root: bisection on the step's dense output (u, h and the seven stages are those of the step)
     const double g0 = u[0] - E.re;
     double lo = 0.0, hi = hit_hi, b[7];
@@ -582,13 +645,14 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
     for (int c = 0; c < DIM; c++) u[c] = y[c];
     status = RT_TERMINATED_EARTH;
     running = false;
-    if (O.save_mode) {
+    if (SAVE) {
       if (MODE != RT_PRESET_RAY3D) {
         rt_extras_at<(MODE == RT_PRESET_RAY3D) ? RT_PRESET_LAT2D : MODE>(E, u, &ex);
       }
-      rt_traj_push<MODE>(S, O, i, cnt, t, u, ex, writer);
+      rt_traj_push<MODE>(O, slot, cnt, staged, truncated, true, t, u, ex, writer);
     }
   }
+  if (SAVE) rt_traj_flush<MODE>(S, O, stage_warp, (int)i, cnt, staged, true, writer);
 
   if (valid && writer) {
 #pragma unroll
@@ -605,6 +669,7 @@ __global__ void __launch_bounds__(RT_BLOCK, COOP ? RT_COOP_MINBLOCKS : RT_MINBLO
     S.nreflect[i] = nreflect;
     S.sgn[i] = sgn_prev;
     S.nsamp[i] = cnt;
+    if (truncated) S.trunc[i] = 1;
     S.status[i] = status;
   }
   rt_enqueue(running && writer, (int)i, idx_out, count_out);

@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
 // There is no CPU fallback anywhere in this file: every compute entry point launches a kernel.
 #include <cuda_runtime.h>
+#include <cub/device/device_scan.cuh>
 
 #include <cstdarg>
 #include <cstdio>
@@ -66,7 +67,14 @@ struct rt_ctx {
   size_t cap_rays = 0;
   int cap_dim = 0;
   double *k1 = nullptr, *h = nullptr, *qold = nullptr, *par = nullptr;
-  int *sgn = nullptr, *nsamp = nullptr, *idx[2] = {nullptr, nullptr}, *count = nullptr;
+  int *sgn = nullptr, *nsamp = nullptr, *trunc = nullptr, *idx[2] = {nullptr, nullptr}, *count = nullptr;
+  // trajectory packing (rt_traj_copy / rt_traj_derived): CSR offsets, scan scratch and the packed rows, grown on demand
+  long long *pack_off = nullptr;
+  size_t pack_off_cap = 0;
+  void *scan_tmp = nullptr;
+  size_t scan_tmp_bytes = 0;
+  double *pack_out = nullptr;
+  size_t pack_out_bytes = 0;
   int *idx_prio[2] = {nullptr, nullptr};  // work lists of the priority chains (chain c's counters: count + 4 c .. + 2)
   cudaStream_t prio_stream = nullptr;     // high-priority stream of the priority chain
   cudaStream_t aux_stream[2] = {nullptr, nullptr};  // second halves of the normal / priority list (chains 2 / 3)
@@ -348,6 +356,8 @@ static void free_work(rt_ctx *ctx) {
   cudaFree(ctx->par);
   cudaFree(ctx->sgn);
   cudaFree(ctx->nsamp);
+  cudaFree(ctx->trunc);
+  ctx->trunc = nullptr;
   cudaFree(ctx->idx[0]);
   cudaFree(ctx->idx[1]);
   cudaFree(ctx->idx_prio[0]);
@@ -365,6 +375,9 @@ extern "C" void rt_destroy(rt_ctx *ctx) {
   cudaStreamSynchronize(ctx->stream);
   free_work(ctx);
   cudaFree(ctx->traj);
+  cudaFree(ctx->pack_off);
+  cudaFree(ctx->scan_tmp);
+  cudaFree(ctx->pack_out);
   cudaFree(ctx->count);
   cudaFree(ctx->stage_d);
   cudaFree(ctx->stage_i);
@@ -410,8 +423,8 @@ extern "C" int rt_set_solver(rt_ctx *ctx, const rt_solver_opts *o) {
   if (o->adaptive && !(o->reltol > 0.0 || o->abstol > 0.0))
     return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: adaptive mode needs a tolerance");
   if (o->nan_policy < 0 || o->nan_policy > 1) return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: nan_policy must be 0 or 1");
-  if (o->save_mode && o->max_samples <= 0)
-    return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: save_mode=1 needs max_samples > 0");
+  if (o->save_mode && o->max_samples < 2)
+    return set_err(ctx, RT_ERR_INVALID, "rt_set_solver: save_mode=1 needs max_samples >= 2 (the start and the final sample)");
   ctx->opts = *o;
   return RT_OK;
 }
@@ -704,6 +717,7 @@ static int ensure_work(rt_ctx *ctx, size_t n, int dim, const RtDevOpts &O, int n
     RT_CUDA(ctx, cudaMalloc(&ctx->par, cap * sizeof(double)));
     RT_CUDA(ctx, cudaMalloc(&ctx->sgn, cap * sizeof(int)));
     RT_CUDA(ctx, cudaMalloc(&ctx->nsamp, cap * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->trunc, cap * sizeof(int)));
     RT_CUDA(ctx, cudaMalloc(&ctx->idx[0], cap * sizeof(int)));
     RT_CUDA(ctx, cudaMalloc(&ctx->idx[1], cap * sizeof(int)));
     RT_CUDA(ctx, cudaMalloc(&ctx->idx_prio[0], cap * sizeof(int)));
@@ -779,16 +793,21 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   S.nreflect = R.nreflect;
   S.sgn = ctx->sgn;
   S.nsamp = ctx->nsamp;
+  S.trunc = ctx->trunc;
   S.traj = ctx->traj;
   cudaStream_t st = ctx->stream;
-  const size_t smem = (size_t)7 * DIM * RT_BLOCK * sizeof(double);
+  // stage derivatives k[7][DIM][thread] and, when trajectories are saved, RT_STAGE staged rows per thread
+  const size_t smem = (size_t)(7 * DIM + (O.save_mode ? RT_STAGE * NCOL : 0)) * RT_BLOCK * sizeof(double);
   // the long rays' one-thread-per-ray launches may ask for more shared memory than they use, so that an SM hosting one
   // of their blocks takes fewer bulk blocks beside it (see the chain loop)
   static const long long prio_smem_kb = getenv("RT_PRIO_SMEM_KB") ? atoll(getenv("RT_PRIO_SMEM_KB")) : 0;
   static const long long prio_smem_rays = getenv("RT_PRIO_SMEM_RAYS") ? atoll(getenv("RT_PRIO_SMEM_RAYS")) : 19000;
   const size_t smem_prio = (size_t)prio_smem_kb * 1024 > smem ? (size_t)prio_smem_kb * 1024 : smem;
-  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_prio));
-  RT_CUDA(ctx, cudaFuncSetAttribute(rt_integrate_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // (kernel variants: one thread / 3 lanes per ray, without / with trajectory staging)
+  auto k1 = O.save_mode ? rt_integrate_kernel<MODE, false, true> : rt_integrate_kernel<MODE, false, false>;
+  auto k3 = O.save_mode ? rt_integrate_kernel<MODE, true, true> : rt_integrate_kernel<MODE, true, false>;
+  RT_CUDA(ctx, cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_prio));
+  RT_CUDA(ctx, cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
   const int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 4;
@@ -950,12 +969,12 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         for (int b = 0; b < batch; b++, C.k++) {
           const int k = C.k;
           if (coop)
-            rt_integrate_kernel<MODE, true><<<grid_for(C.upper, (RT_BLOCK / 32) * RT_COOP_RAYS_PER_WARP), RT_BLOCK, smem, C.st>>>(
+            k3<<<grid_for(C.upper, (RT_BLOCK / 32) * RT_COOP_RAYS_PER_WARP), RT_BLOCK, smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           else
-            rt_integrate_kernel<MODE, false><<<grid_for(C.upper, RT_BLOCK), RT_BLOCK,
-                                               ((c & 1) && ch[1].upper + ch[3].upper <= prio_smem_rays) ? smem_prio : smem, C.st>>>(
+            k1<<<grid_for(C.upper, RT_BLOCK), RT_BLOCK,
+                 ((c & 1) && ch[1].upper + ch[3].upper <= prio_smem_rays) ? smem_prio : smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           C.cur ^= 1;
@@ -1274,60 +1293,118 @@ extern "C" int rt_traj_columns(const rt_ctx *ctx) {
   return ctx->env.preset == RT_PRESET_RAY3D ? 8 : 9;
 }
 
-extern "C" int rt_traj_size(rt_ctx *ctx, int64_t *total) {
-  if (!ctx || !total) return set_err(ctx, RT_ERR_INVALID, "rt_traj_size: null argument");
+static int traj_ready(rt_ctx *ctx, const char *who) {
+  if (!ctx) return set_err(ctx, RT_ERR_INVALID, "%s: null context", who);
   if (ctx->last_mode < 0 || ctx->last_max_samples <= 0)
-    return set_err(ctx, RT_ERR_STATE, "rt_traj_size: the last solve did not save trajectories (save_mode = 0)");
+    return set_err(ctx, RT_ERR_STATE, "%s: the last solve did not save trajectories (save_mode = 0)", who);
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
-  std::vector<int> ns((size_t)ctx->last_n);
-  RT_CUDA(ctx, cudaMemcpyAsync(ns.data(), ctx->nsamp, ns.size() * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  int64_t s = 0;
-  for (int v : ns) s += v;
-  *total = s;
   return RT_OK;
 }
 
-// gather rows [n][cap][ncol] -> packed [total][ncol] using CSR offsets
-__global__ void rt_traj_pack_kernel(long long n, int cap, int ncol, const double *traj, const long long *offsets,
-                                    double *out) {
-  long long ray = blockIdx.x;
-  long long lo = offsets[ray], cnt = offsets[ray + 1] - lo;
-  const double *src = traj + (size_t)ray * cap * ncol;
-  double *dst = out + (size_t)lo * ncol;
-  for (long long k = threadIdx.x; k < cnt * ncol; k += blockDim.x) dst[k] = src[k];
+// CSR offsets of the last solve's trajectories on the device: pack_off[0..n] = exclusive prefix sum of nsamp (cub scan)
+static int traj_offsets_device(rt_ctx *ctx) {
+  const long long n = ctx->last_n;
+  if ((size_t)(n + 1) > ctx->pack_off_cap) {
+    cudaFree(ctx->pack_off);
+    ctx->pack_off = nullptr;
+    ctx->pack_off_cap = 0;
+    RT_CUDA(ctx, cudaMalloc(&ctx->pack_off, (size_t)(n + 1) * sizeof(long long)));
+    ctx->pack_off_cap = (size_t)(n + 1);
+  }
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->pack_off, 0, sizeof(long long), ctx->stream));
+  if (n == 0) return RT_OK;
+  size_t need = 0;
+  RT_CUDA(ctx, cub::DeviceScan::InclusiveSum(nullptr, need, ctx->nsamp, ctx->pack_off + 1, (int)n, ctx->stream));
+  if (need > ctx->scan_tmp_bytes) {
+    cudaFree(ctx->scan_tmp);
+    ctx->scan_tmp = nullptr;
+    ctx->scan_tmp_bytes = 0;
+    RT_CUDA(ctx, cudaMalloc(&ctx->scan_tmp, need));
+    ctx->scan_tmp_bytes = need;
+  }
+  RT_CUDA(ctx, cub::DeviceScan::InclusiveSum(ctx->scan_tmp, need, ctx->nsamp, ctx->pack_off + 1, (int)n, ctx->stream));
+  return RT_OK;
+}
+
+static int ensure_pack_out(rt_ctx *ctx, size_t bytes) {
+  if (bytes > ctx->pack_out_bytes) {
+    cudaFree(ctx->pack_out);
+    ctx->pack_out = nullptr;
+    ctx->pack_out_bytes = 0;
+    cudaError_t e = cudaMalloc(&ctx->pack_out, bytes);
+    if (e != cudaSuccess) return set_err(ctx, RT_ERR_NOMEM, "trajectory packing: %s (%zu bytes)", cudaGetErrorString(e), bytes);
+    ctx->pack_out_bytes = bytes;
+  }
+  return RT_OK;
+}
+
+extern "C" int rt_traj_size(rt_ctx *ctx, int64_t *total) {
+  if (!total) return set_err(ctx, RT_ERR_INVALID, "rt_traj_size: null argument");
+  if (int rc = traj_ready(ctx, "rt_traj_size")) return rc;
+  if (int rc = traj_offsets_device(ctx)) return rc;
+  long long t = 0;
+  RT_CUDA(ctx, cudaMemcpyAsync(&t, ctx->pack_off + ctx->last_n, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *total = t;
+  return RT_OK;
+}
+
+// 1 where a trajectory did not fit max_samples (samples were dropped before its final one), flags[n]
+extern "C" int rt_traj_truncated(rt_ctx *ctx, int32_t *flags) {
+  if (!flags) return set_err(ctx, RT_ERR_INVALID, "rt_traj_truncated: null argument");
+  if (int rc = traj_ready(ctx, "rt_traj_truncated")) return rc;
+  if (ctx->last_n == 0) return RT_OK;
+  RT_CUDA(ctx, cudaMemcpyAsync(flags, ctx->trunc, (size_t)ctx->last_n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
+// rows [n][cap][ncol] -> packed [total][ncol] by the CSR offsets: a ray's rows are contiguous on both sides, so each
+// block streams one ray's cnt * ncol doubles (coalesced loads and stores; the grid strides over the rays)
+__global__ void __launch_bounds__(256) rt_traj_pack_kernel(long long n, int cap, int ncol, const double *__restrict__ traj,
+                                                           const long long *__restrict__ offsets, double *__restrict__ out) {
+  for (long long ray = blockIdx.x; ray < n; ray += gridDim.x) {
+    const long long lo = offsets[ray], len = (offsets[ray + 1] - lo) * ncol;
+    const double *src = traj + (size_t)ray * cap * ncol;
+    double *dst = out + (size_t)lo * ncol;
+    for (long long k = threadIdx.x; k < len; k += blockDim.x) dst[k] = src[k];
+  }
+}
+
+static unsigned pack_grid(long long n) { return (unsigned)(n < 148LL * 64 ? (n > 0 ? n : 1) : 148LL * 64); }
+
+// packed rows and offsets in DEVICE memory (owned by the context until the next solve / packing call)
+extern "C" int rt_traj_pack_device(rt_ctx *ctx, const int64_t **d_offsets, const double **d_samples, int64_t *total) {
+  if (int rc = traj_ready(ctx, "rt_traj_pack_device")) return rc;
+  if (int rc = traj_offsets_device(ctx)) return rc;
+  const long long n = ctx->last_n;
+  const int ncol = ctx->last_mode == RT_PRESET_RAY3D ? 8 : 9;
+  long long t = 0;
+  RT_CUDA(ctx, cudaMemcpyAsync(&t, ctx->pack_off + n, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (int rc = ensure_pack_out(ctx, (size_t)(t > 0 ? t : 1) * ncol * sizeof(double))) return rc;
+  if (t > 0) {
+    rt_traj_pack_kernel<<<pack_grid(n), 256, 0, ctx->stream>>>(n, ctx->last_max_samples, ncol, ctx->traj, ctx->pack_off, ctx->pack_out);
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+  if (d_offsets) *d_offsets = (const int64_t *)ctx->pack_off;
+  if (d_samples) *d_samples = ctx->pack_out;
+  if (total) *total = t;
+  return RT_OK;
 }
 
 extern "C" int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples) {
-  if (!ctx || !offsets || !samples) return set_err(ctx, RT_ERR_INVALID, "rt_traj_copy: null argument");
-  if (ctx->last_mode < 0 || ctx->last_max_samples <= 0)
-    return set_err(ctx, RT_ERR_STATE, "rt_traj_copy: the last solve did not save trajectories (save_mode = 0)");
-  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!offsets || !samples) return set_err(ctx, RT_ERR_INVALID, "rt_traj_copy: null argument");
+  int64_t total = 0;
+  if (int rc = rt_traj_pack_device(ctx, nullptr, nullptr, &total)) return rc;
   const long long n = ctx->last_n;
   const int ncol = ctx->last_mode == RT_PRESET_RAY3D ? 8 : 9;
-  std::vector<int> ns((size_t)n);
-  RT_CUDA(ctx, cudaMemcpyAsync(ns.data(), ctx->nsamp, ns.size() * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaMemcpyAsync(offsets, ctx->pack_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+  if (total > 0)
+    RT_CUDA(ctx, cudaMemcpyAsync(samples, ctx->pack_out, (size_t)total * ncol * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  offsets[0] = 0;
-  for (long long i = 0; i < n; i++) offsets[i + 1] = offsets[i] + ns[(size_t)i];
-  const int64_t total = offsets[n];
-  if (total == 0) return RT_OK;
-  long long *d_off = nullptr;
-  double *d_out = nullptr;
-  RT_CUDA(ctx, cudaMalloc(&d_off, (size_t)(n + 1) * sizeof(long long)));
-  cudaError_t e = cudaMalloc(&d_out, (size_t)total * ncol * sizeof(double));
-  if (e != cudaSuccess) {
-    cudaFree(d_off);
-    return set_err(ctx, RT_ERR_NOMEM, "rt_traj_copy: %s", cudaGetErrorString(e));
-  }
-  static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
-  cudaMemcpyAsync(d_off, offsets, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream);
-  rt_traj_pack_kernel<<<(unsigned)n, 64, 0, ctx->stream>>>(n, ctx->last_max_samples, ncol, ctx->traj, d_off, d_out);
-  cudaMemcpyAsync(samples, d_out, (size_t)total * ncol * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
-  e = cudaStreamSynchronize(ctx->stream);
-  cudaFree(d_off);
-  cudaFree(d_out);
-  if (e != cudaSuccess) return set_err(ctx, RT_ERR_CUDA, "rt_traj_copy: %s", cudaGetErrorString(e));
   return RT_OK;
 }
 
@@ -1336,32 +1413,33 @@ extern "C" int rt_traj_copy(rt_ctx *ctx, int64_t *offsets, double *samples) {
 // colatitude presets: x = r sin(theta), y = r cos(theta), RayMain.jl:400-401, scratch.jl:407-408),
 // dt[i] = t[i+1] - t[i] with a trailing 0 (RayTrace_lat.jl:369-372).  3D [EXT]: x = r sin(theta) cos(phi),
 // y = r sin(theta) sin(phi), z = r cos(theta).  Packed like rt_traj_copy: out[offsets[ray] + k][3 or 4].
-__global__ void rt_traj_derived_kernel(long long n, int cap, int ncol, int mode, const double *traj,
-                                       const long long *offsets, double *out) {
-  const long long ray = blockIdx.x;
-  const long long lo = offsets[ray], cnt = offsets[ray + 1] - lo;
-  const double *src = traj + (size_t)ray * cap * ncol;
+__global__ void __launch_bounds__(128) rt_traj_derived_kernel(long long n, int cap, int ncol, int mode, const double *traj,
+                                                              const long long *offsets, double *out) {
   const int nd = (mode == RT_PRESET_RAY3D) ? 4 : 3;
-  for (long long k = threadIdx.x; k < cnt; k += blockDim.x) {
-    const double *row = src + (size_t)k * ncol;
-    const double t = row[0], r = row[1], a = row[2];
-    double *o = out + (size_t)(lo + k) * nd;
-    double sa, ca;
-    rt_sincos(a, &sa, &ca);
-    if (mode == RT_PRESET_RAY3D) {
-      double sp, cp;
-      rt_sincos(row[3], &sp, &cp);
-      o[0] = (r * sa) * cp;
-      o[1] = (r * sa) * sp;
-      o[2] = r * ca;
-    } else if (mode == RT_PRESET_LAT2D) {
-      o[0] = r * ca;
-      o[1] = r * sa;
-    } else {
-      o[0] = r * sa;
-      o[1] = r * ca;
+  for (long long ray = blockIdx.x; ray < n; ray += gridDim.x) {
+    const long long lo = offsets[ray], cnt = offsets[ray + 1] - lo;
+    const double *src = traj + (size_t)ray * cap * ncol;
+    for (long long k = threadIdx.x; k < cnt; k += blockDim.x) {
+      const double *row = src + (size_t)k * ncol;
+      const double t = row[0], r = row[1], a = row[2];
+      double *o = out + (size_t)(lo + k) * nd;
+      double sa, ca;
+      rt_sincos(a, &sa, &ca);
+      if (mode == RT_PRESET_RAY3D) {
+        double sp, cp;
+        rt_sincos(row[3], &sp, &cp);
+        o[0] = (r * sa) * cp;
+        o[1] = (r * sa) * sp;
+        o[2] = r * ca;
+      } else if (mode == RT_PRESET_LAT2D) {
+        o[0] = r * ca;
+        o[1] = r * sa;
+      } else {
+        o[0] = r * sa;
+        o[1] = r * ca;
+      }
+      o[nd - 1] = (k + 1 < cnt) ? src[(size_t)(k + 1) * ncol] - t : 0.0;
     }
-    o[nd - 1] = (k + 1 < cnt) ? src[(size_t)(k + 1) * ncol] - t : 0.0;
   }
 }
 
@@ -1370,31 +1448,22 @@ extern "C" int rt_traj_derived_columns(rt_ctx *ctx) {
   return ctx->env.preset == RT_PRESET_RAY3D ? 4 : 3;
 }
 
+// `offsets` (as returned by rt_traj_copy) is accepted for the caller's convenience; the device-side offsets of the last
+// solve are what the kernel uses
 extern "C" int rt_traj_derived(rt_ctx *ctx, const int64_t *offsets, double *out) {
-  if (!ctx || !offsets || !out) return set_err(ctx, RT_ERR_INVALID, "rt_traj_derived: null argument");
-  if (ctx->last_mode < 0 || ctx->last_max_samples <= 0)
-    return set_err(ctx, RT_ERR_STATE, "rt_traj_derived: the last solve did not save trajectories (save_mode = 0)");
-  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!offsets || !out) return set_err(ctx, RT_ERR_INVALID, "rt_traj_derived: null argument");
+  if (int rc = traj_ready(ctx, "rt_traj_derived")) return rc;
+  if (int rc = traj_offsets_device(ctx)) return rc;
   const long long n = ctx->last_n;
   const int ncol = ctx->last_mode == RT_PRESET_RAY3D ? 8 : 9, nd = ctx->last_mode == RT_PRESET_RAY3D ? 4 : 3;
   const int64_t total = offsets[n];
   if (total == 0) return RT_OK;
-  long long *d_off = nullptr;
-  double *d_out = nullptr;
-  RT_CUDA(ctx, cudaMalloc(&d_off, (size_t)(n + 1) * sizeof(long long)));
-  cudaError_t e = cudaMalloc(&d_out, (size_t)total * nd * sizeof(double));
-  if (e != cudaSuccess) {
-    cudaFree(d_off);
-    return set_err(ctx, RT_ERR_NOMEM, "rt_traj_derived: %s", cudaGetErrorString(e));
-  }
-  cudaMemcpyAsync(d_off, offsets, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream);
-  rt_traj_derived_kernel<<<(unsigned)n, 64, 0, ctx->stream>>>(n, ctx->last_max_samples, ncol, ctx->last_mode, ctx->traj,
-                                                             d_off, d_out);
-  cudaMemcpyAsync(out, d_out, (size_t)total * nd * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
-  e = cudaStreamSynchronize(ctx->stream);
-  cudaFree(d_off);
-  cudaFree(d_out);
-  if (e != cudaSuccess) return set_err(ctx, RT_ERR_CUDA, "rt_traj_derived: %s", cudaGetErrorString(e));
+  if (int rc = ensure_pack_out(ctx, (size_t)total * nd * sizeof(double))) return rc;
+  rt_traj_derived_kernel<<<pack_grid(n), 128, 0, ctx->stream>>>(n, ctx->last_max_samples, ncol, ctx->last_mode, ctx->traj,
+                                                                ctx->pack_off, ctx->pack_out);
+  RT_CUDA(ctx, cudaGetLastError());
+  RT_CUDA(ctx, cudaMemcpyAsync(out, ctx->pack_out, (size_t)total * nd * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return RT_OK;
 }
 

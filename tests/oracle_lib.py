@@ -134,8 +134,8 @@ def haselgrove_3d(E, u, f):
 
 
 class RayOut:
-    def __init__(self, u_end, t_end, ints, traj):
-        self.u_end, self.t_end = u_end, t_end
+    def __init__(self, u_end, t_end, ints, traj, truncated=False):
+        self.u_end, self.t_end, self.truncated = u_end, t_end, truncated
         self.status, self.naccept, self.nreject, self.nfe, self.nreflect = [int(v) for v in ints]
         self.traj = traj
 
@@ -147,7 +147,7 @@ def solve_ray_2d(E, o, u0, t0=0.0, cap=0):
     ns = C.c_int64(0)
     lib().orc_solve_ray_2d(C.byref(E), C.byref(o), _p(u0), _d(t0), _p(ue), C.byref(te), _p(ints),
                            _p(traj) if cap else None, C.c_int64(cap), C.byref(ns))
-    return RayOut(ue, te.value, ints, traj[: ns.value] if cap else None)
+    return RayOut(ue, te.value, ints, traj[: abs(ns.value)] if cap else None, ns.value < 0)
 
 
 def solve_ray_3d(E, o, u0, f, t0=0.0, cap=0):
@@ -157,7 +157,7 @@ def solve_ray_3d(E, o, u0, f, t0=0.0, cap=0):
     ns = C.c_int64(0)
     lib().orc_solve_ray_3d(C.byref(E), C.byref(o), _p(u0), _d(f), _d(t0), _p(ue), C.byref(te), _p(ints),
                            _p(traj) if cap else None, C.c_int64(cap), C.byref(ns))
-    return RayOut(ue, te.value, ints, traj[: ns.value] if cap else None)
+    return RayOut(ue, te.value, ints, traj[: abs(ns.value)] if cap else None, ns.value < 0)
 
 
 def solve_batch(E, o, launch, dim3, nthreads=1):
@@ -181,7 +181,7 @@ def solve_test_ode(which, o, u0, t0=0.0, re_evt=0.0, cap=0):
     ns = C.c_int64(0)
     lib().orc_solve_test_ode(C.c_int(which), C.byref(o), _p(u0), _d(t0), _d(re_evt), _p(ue), C.byref(te),
                              _p(ints), _p(traj) if cap else None, C.c_int64(cap), C.byref(ns))
-    return RayOut(ue, te.value, ints, traj[: ns.value] if cap else None)
+    return RayOut(ue, te.value, ints, traj[: abs(ns.value)] if cap else None, ns.value < 0)
 
 
 def interior_events(reset=False):

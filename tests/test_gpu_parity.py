@@ -546,3 +546,57 @@ def test_multi_gpu_entry_point_block_cyclic_partition():
     res = m2.solve(launch)
     m2.close()
     _check_solve(res, O.solve_batch(O.env(O.LAT2D), O.opts(maxiters=150), launch, False, 4), 1e-10)
+
+
+@pytest.mark.parametrize("coop", [-1, 10 ** 9])
+def test_trajectory_truncation_keeps_final_sample_and_matches_oracle(coop):
+    """max_samples smaller than the ray's step count (staged rows, warp flush, reserved final row): the kept rows and
+    the truncation flags equal the oracle's; slices of 3 attempts leave partial stages at every launch boundary."""
+    launch = sweeps.sweep_3d(3, 2, 7)
+    E, cap = O.env(O.RAY3D), 12
+    rt = R.RayTracer("ray3d")
+    rt.set_solver(save_mode=1, max_samples=cap, save_stride=1, slice_attempts=3, coop_threshold=coop, r_esc=10 * RE)
+    res = rt.solve(launch)
+    o = O.opts(reltol=1e-3, dtmax=0, dtmin=0, save_mode=1, max_samples=cap, r_esc=10 * RE)
+    ntr = 0
+    for k in range(launch.shape[1]):
+        ref = O.solve_ray_3d(E, o, launch[:7, k], launch[7, k], launch[8, k], cap=cap)
+        assert _same(res.trajectory(k), ref.traj), k
+        assert bool(res.truncated[k]) == ref.truncated, k
+        if ref.truncated:
+            ntr += 1
+            assert ref.traj.shape[0] == cap and res.trajectory(k)[-1, 0] == res.t_end[k]  # the event row survived
+    assert ntr > launch.shape[1] // 2
+    rt.close()
+    launch = sweeps.sweep_2d(5, 3)
+    rt = R.RayTracer("lat2d")
+    rt.set_solver(t1=3.0e8, save_mode=1, max_samples=40, save_stride=2, slice_attempts=5, coop_threshold=coop)
+    res = rt.solve(launch)
+    E2, o2 = O.env(O.LAT2D), O.opts(t1=3.0e8, save_mode=1, max_samples=40, save_stride=2)
+    for k in range(launch.shape[1]):
+        ref = O.solve_ray_2d(E2, o2, launch[:4, k], launch[4, k], cap=40)
+        assert _same(res.trajectory(k), ref.traj) and bool(res.truncated[k]) == ref.truncated, k
+    assert res.truncated.any()
+    rt.close()
+
+
+def test_trajectory_pack_on_the_device_and_bad_capacity():
+    import ctypes as C
+    import torch
+    launch = sweeps.sweep_3d(6, 5, 8)
+    rt = R.RayTracer("ray3d")
+    rt.set_solver(save_mode=1, max_samples=128, r_esc=10 * RE)
+    res = rt.solve(launch)
+    d_off, d_rows, total = C.c_void_p(), C.c_void_p(), C.c_int64()
+    assert R.api._lib().rt_traj_pack_device(rt._ctx, C.byref(d_off), C.byref(d_rows), C.byref(total)) == 0
+    assert total.value == res.traj.shape[0] == res.traj_offsets[-1]
+    off = np.zeros(launch.shape[1] + 1, np.int64)
+    rows = np.zeros((total.value, 8))
+    cudart = C.CDLL("libcudart.so.12")
+    assert cudart.cudaMemcpy(off.ctypes.data_as(C.c_void_p), d_off, C.c_size_t(off.nbytes), C.c_int(2)) == 0
+    assert cudart.cudaMemcpy(rows.ctypes.data_as(C.c_void_p), d_rows, C.c_size_t(rows.nbytes), C.c_int(2)) == 0
+    assert np.array_equal(off, res.traj_offsets) and _same(rows, res.traj)
+    assert not res.truncated.any()
+    with pytest.raises(RuntimeError, match="max_samples >= 2"):
+        rt.set_solver(save_mode=1, max_samples=1)
+    rt.close()

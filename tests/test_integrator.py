@@ -111,3 +111,17 @@ def test_reference_ray_cfg1():
     assert r.traj.shape == (r.naccept + 1, 9)
     gd = r.u_end[3] - 1000.0  # slot-4 dual use: group delay = u4 - f0 (RayTrace_lat.jl:257,273)
     assert 0.3 < gd < 0.4
+
+
+def test_trajectory_capacity_keeps_the_final_sample_and_flags_truncation():
+    """max_samples too small: rows 0 .. cap-2 are the first regular samples, the last row is the final sample (event
+    point / tspan end), and the ray is flagged (no silent loss of the end of a trajectory)."""
+    o = O.opts(reltol=1e-9, abstol=1e-9, dtmax=0, dtmin=0, t1=10.0)
+    full = O.solve_test_ode(0, o, [1.0, 0.0], re_evt=0.5, cap=4096)
+    assert not full.truncated and full.traj.shape[0] == full.naccept + 1
+    cut = O.solve_test_ode(0, o, [1.0, 0.0], re_evt=0.5, cap=10)
+    assert cut.truncated and cut.traj.shape[0] == 10
+    assert np.array_equal(cut.traj[:9], full.traj[:9]) and np.array_equal(cut.traj[9], full.traj[-1])
+    assert cut.traj[9, 0] == cut.t_end and cut.status == 2
+    fit = O.solve_test_ode(0, o, [1.0, 0.0], re_evt=0.5, cap=full.traj.shape[0])  # exactly fits: not truncated
+    assert not fit.truncated and np.array_equal(fit.traj, full.traj)
