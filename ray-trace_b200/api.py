@@ -59,30 +59,44 @@ class Stats(C.Structure):
 
 
 _LIB = None
+_LIB_DEV = None
 
 
 def lib_path():
     return _build.LIB
 
 
+def _load(path):
+    if not os.path.exists(path):
+        raise ImportError(
+            f"{path} is missing: build it with `python ray-trace_b200/build.py` (needs nvcc). "
+            "There is no CPU fallback.")
+    L = C.CDLL(path)
+    L.rt_last_error.restype = C.c_char_p
+    L.rt_last_error.argtypes = [C.c_void_p]
+    return L
+
+
 def _lib():
+    """The product library: the reference-facing C ABI and nothing else."""
     global _LIB
     if _LIB is None:
-        path = lib_path()
-        if not os.path.exists(path):
-            raise ImportError(
-                f"{path} is missing: build it with `python ray-trace_b200/build.py` (needs nvcc). "
-                "There is no CPU fallback.")
-        L = C.CDLL(path)
-        L.rt_last_error.restype = C.c_char_p
-        L.rt_last_error.argtypes = [C.c_void_p]
-        _LIB = L
+        _LIB = _load(lib_path())
     return _LIB
 
 
-def _check(rc, ctx=None):
+def _dev_lib():
+    """The -DRT_DEV build of the same sources: + diagnostics (include/raytrace_b200_dev.h) and environment switches.
+    Only diagnostics tests and tools/ use it (RayTracer(..., dev=True))."""
+    global _LIB_DEV
+    if _LIB_DEV is None:
+        _LIB_DEV = _load(_build.LIB_DEV)
+    return _LIB_DEV
+
+
+def _check(rc, ctx=None, lib=None):
     if rc != 0:
-        msg = _lib().rt_last_error(ctx).decode() if True else ""
+        msg = (lib or _lib()).rt_last_error(ctx).decode()
         raise RuntimeError(f"raytrace_b200 error {rc}: {msg}")
 
 
@@ -157,9 +171,10 @@ class SolveResult:
 class RayTracer:
     """One context = one GPU + one environment preset + solver options."""
 
-    def __init__(self, preset="lat2d", device=0, env=None, opts=None):
+    def __init__(self, preset="lat2d", device=0, env=None, opts=None, dev=False):
         self._ctx = C.c_void_p()
-        _check(_lib().rt_create(C.byref(self._ctx), C.c_int(device)))
+        self._L = _dev_lib() if dev else _lib()
+        _check(self._L.rt_create(C.byref(self._ctx), C.c_int(device)), lib=self._L)
         self.preset = _preset_id(preset)
         self.env = env if env is not None else env_preset(self.preset)
         self.opts = opts if opts is not None else solver_preset(self.preset)
@@ -168,7 +183,7 @@ class RayTracer:
 
     def close(self):
         if self._ctx:
-            _lib().rt_destroy(self._ctx)
+            self._L.rt_destroy(self._ctx)
             self._ctx = C.c_void_p()
 
     def __del__(self):
@@ -182,27 +197,27 @@ class RayTracer:
         return 7 if self.env.preset == 1 else 4
 
     def set_env(self, env):
-        _check(_lib().rt_set_env(self._ctx, C.byref(env)), self._ctx)
+        _check(self._L.rt_set_env(self._ctx, C.byref(env)), self._ctx, self._L)
         self.env = env
 
     def set_solver(self, opts=None, **kw):
         o = opts if opts is not None else self.opts
         for k, v in kw.items():
             setattr(o, k, v)
-        _check(_lib().rt_set_solver(self._ctx, C.byref(o)), self._ctx)
+        _check(self._L.rt_set_solver(self._ctx, C.byref(o)), self._ctx, self._L)
         self.opts = o
 
     def set_stream(self, cuda_stream_ptr):
-        _check(_lib().rt_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr)), self._ctx)
+        _check(self._L.rt_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr)), self._ctx, self._L)
 
     def stats(self):
         s = Stats()
-        _check(_lib().rt_get_stats(self._ctx, C.byref(s)), self._ctx)
+        _check(self._L.rt_get_stats(self._ctx, C.byref(s)), self._ctx, self._L)
         return s
 
     def measure_fp64_peak(self):
         v = C.c_double()
-        _check(_lib().rt_measure_fp64_peak(self._ctx, C.byref(v)), self._ctx)
+        _check(self._L.rt_measure_fp64_peak(self._ctx, C.byref(v)), self._ctx, self._L)
         return v.value
 
     # -- reference function names, batched ---------------------------------------------------------
@@ -212,8 +227,8 @@ class RayTracer:
         n = max(np.size(r), np.size(lam), np.size(chi), np.size(freq))
         r, lam, chi, freq = _f64(r, n), _f64(lam, n), _f64(chi, n), _f64(freq, n)
         mu, dmu = np.zeros(n), np.zeros(n)
-        _check(_lib().rt_phase_refractive_index_2d(self._ctx, C.c_int64(n), _ptr(r), _ptr(lam), _ptr(chi), _ptr(freq),
-                                                   _ptr(mu), _ptr(dmu)), self._ctx)
+        _check(self._L.rt_phase_refractive_index_2d(self._ctx, C.c_int64(n), _ptr(r), _ptr(lam), _ptr(chi), _ptr(freq),
+                                                   _ptr(mu), _ptr(dmu)), self._ctx, self._L)
         return mu, dmu
 
     def refractive_index(self, r, th, ph, rho_r, rho_th, rho_ph, freq):
@@ -222,8 +237,8 @@ class RayTracer:
         n = max(np.size(a) for a in args)
         a = [_f64(x, n) for x in args]
         mu, dmu, psi, b = np.zeros(n), np.zeros(n), np.zeros(n), np.zeros((3, n))
-        _check(_lib().rt_refractive_index_3d(self._ctx, C.c_int64(n), *[_ptr(x) for x in a], _ptr(mu), _ptr(dmu),
-                                             _ptr(psi), _ptr(b)), self._ctx)
+        _check(self._L.rt_refractive_index_3d(self._ctx, C.c_int64(n), *[_ptr(x) for x in a], _ptr(mu), _ptr(dmu),
+                                             _ptr(psi), _ptr(b)), self._ctx, self._L)
         return mu, dmu, psi, b
 
     def haselgrove(self, u, p=None, t=None):
@@ -235,9 +250,9 @@ class RayTracer:
         du = np.zeros_like(u2)
         if self.dim == 7:
             f = _f64(p[0] if isinstance(p, (list, tuple)) else p, n)
-            _check(_lib().rt_haselgrove_3d(self._ctx, C.c_int64(n), _ptr(u2), _ptr(f), _ptr(du)), self._ctx)
+            _check(self._L.rt_haselgrove_3d(self._ctx, C.c_int64(n), _ptr(u2), _ptr(f), _ptr(du)), self._ctx, self._L)
         else:
-            _check(_lib().rt_haselgrove_2d(self._ctx, C.c_int64(n), _ptr(u2), _ptr(du)), self._ctx)
+            _check(self._L.rt_haselgrove_2d(self._ctx, C.c_int64(n), _ptr(u2), _ptr(du)), self._ctx, self._L)
         return du[:, 0] if single else du
 
     def plasmasphere(self, r, lam):
@@ -246,7 +261,7 @@ class RayTracer:
         n = max(np.size(r), np.size(lam))
         r, lam = _f64(r, n), _f64(lam, n)
         out = np.zeros((5, n))
-        _check(_lib().rt_plasmasphere_density(self._ctx, C.c_int64(n), _ptr(r), _ptr(lam), _ptr(out)), self._ctx)
+        _check(self._L.rt_plasmasphere_density(self._ctx, C.c_int64(n), _ptr(r), _ptr(lam), _ptr(out)), self._ctx, self._L)
         return dict(zip(("L", "plasmasphere_eq", "diffusive_equilibrium", "ionosphere_eq", "ne_total"), out))
 
     def meridian_maps(self, x, y):
@@ -255,7 +270,7 @@ class RayTracer:
         x = np.ascontiguousarray(np.asarray(x, dtype=np.float64))
         y = np.ascontiguousarray(np.asarray(y, dtype=np.float64))
         out = np.zeros((4, x.size * y.size))
-        _check(_lib().rt_meridian_maps(self._ctx, C.c_int64(x.size), C.c_int64(y.size), _ptr(x), _ptr(y), _ptr(out)), self._ctx)
+        _check(self._L.rt_meridian_maps(self._ctx, C.c_int64(x.size), C.c_int64(y.size), _ptr(x), _ptr(y), _ptr(out)), self._ctx, self._L)
         return {k: out[i].reshape(x.size, y.size) for i, k in enumerate(("L", "ne_total", "log10_ne_total", "Bmag"))}
 
     def debug_rhs3d(self, u, freq):
@@ -267,8 +282,8 @@ class RayTracer:
         n = u.shape[0]
         inp = np.ascontiguousarray(np.concatenate([u, _f64(freq, n)[:, None]], axis=1))
         df, de, ok = np.zeros((n, 7)), np.zeros((n, 7)), np.zeros(n, dtype=np.int32)
-        _check(_lib().rt_debug_rhs3d(self._ctx, C.c_int(n), _ptr(inp), _ptr(df), ok.ctypes.data_as(C.c_void_p), _ptr(de)),
-               self._ctx)
+        _check(self._L.rt_debug_rhs3d(self._ctx, C.c_int(n), _ptr(inp), _ptr(df), ok.ctypes.data_as(C.c_void_p), _ptr(de)),
+               self._ctx, self._L)
         return df, ok.astype(bool), de
 
     # -- the solve ---------------------------------------------------------------------------------
@@ -282,22 +297,22 @@ class RayTracer:
         res = SolveResult(n, self.dim)
         cres = res._c()
         cols = [_ptr(launch[k]) for k in range(ncol)]
-        fn = _lib().rt_solve_3d if self.dim == 7 else _lib().rt_solve_2d
-        _check(fn(self._ctx, C.c_int64(n), *cols, C.byref(cres)), self._ctx)
+        fn = self._L.rt_solve_3d if self.dim == 7 else self._L.rt_solve_2d
+        _check(fn(self._ctx, C.c_int64(n), *cols, C.byref(cres)), self._ctx, self._L)
         res.stats = self.stats()
         want = self.opts.save_mode if with_trajectories is None else with_trajectories
         if want and self.opts.save_mode and n > 0:
             total = C.c_int64()
-            _check(_lib().rt_traj_size(self._ctx, C.byref(total)), self._ctx)
-            ncolt = _lib().rt_traj_columns(self._ctx)
+            _check(self._L.rt_traj_size(self._ctx, C.byref(total)), self._ctx, self._L)
+            ncolt = self._L.rt_traj_columns(self._ctx)
             res.traj_offsets = np.zeros(n + 1, np.int64)
             res.traj = np.zeros((total.value, ncolt))
-            _check(_lib().rt_traj_copy(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj)), self._ctx)
+            _check(self._L.rt_traj_copy(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj)), self._ctx, self._L)
             res.truncated = np.zeros(n, np.int32)
-            _check(_lib().rt_traj_truncated(self._ctx, _ptr(res.truncated)), self._ctx)
+            _check(self._L.rt_traj_truncated(self._ctx, _ptr(res.truncated)), self._ctx, self._L)
             if derived:  # Cartesian track and step sizes, computed on the device (RayTrace_lat.jl:351-352,369-372)
-                res.traj_derived = np.zeros((total.value, _lib().rt_traj_derived_columns(self._ctx)))
-                _check(_lib().rt_traj_derived(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj_derived)), self._ctx)
+                res.traj_derived = np.zeros((total.value, self._L.rt_traj_derived_columns(self._ctx)))
+                _check(self._L.rt_traj_derived(self._ctx, _ptr(res.traj_offsets), _ptr(res.traj_derived)), self._ctx, self._L)
         return res
 
 
@@ -522,8 +537,8 @@ def _solve_device(self, n, col_ptrs, res_ptrs):
     """rt_solve_{2d,3d}_device: every pointer is a device address (ints), e.g. torch tensors' data_ptr().
     col_ptrs: 5 (2D) or 9 (3D) launch columns; res_ptrs: dict with the rt_result member names."""
     cres = _Result(*[C.c_void_p(res_ptrs[k]) for k, _ in _Result._fields_])
-    fn = _lib().rt_solve_3d_device if self.dim == 7 else _lib().rt_solve_2d_device
-    _check(fn(self._ctx, C.c_int64(n), *[C.c_void_p(p) for p in col_ptrs], C.byref(cres)), self._ctx)
+    fn = self._L.rt_solve_3d_device if self.dim == 7 else self._L.rt_solve_2d_device
+    _check(fn(self._ctx, C.c_int64(n), *[C.c_void_p(p) for p in col_ptrs], C.byref(cres)), self._ctx, self._L)
     return self.stats()
 
 

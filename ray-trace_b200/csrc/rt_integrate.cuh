@@ -106,16 +106,19 @@ __device__ __noinline__ int rt_event_scan(RtScanIn in) {
 struct RtVec7 { double v[7]; };
 struct RtVec4x { double v[4]; RtExtras2D ex; };
 
-// fallback census (cold path only): [0] calls, [1] r < 2^16 or negative, [2] non-finite input, [3] non-finite result,
-// [4] finite in and out (a guard was merely conservative), [5] 2D calls, [6] r is NaN, [7] |r| < 2^16
+// Exact code, out of line.  The -DRT_DEV build also keeps a census of these calls (cold path only): [0] calls, [1] r < 2^16
+// or negative, [2] non-finite input, [3] non-finite result, [4] finite in and out (a guard was merely conservative),
+// [5] 2D calls, [6] r is NaN, [7] |r| < 2^16; and the first RT_DBG_SAMPLES inputs (3D: u[0..6], freq) since the last reset.
+#ifdef RT_DEV
 __device__ unsigned long long rt_dbg_fallback[8];
-// the first RT_DBG_SAMPLES inputs (3D: u[0..6], freq) that took the exact path since the last reset
 #define RT_DBG_SAMPLES 8192
 __device__ double rt_dbg_sample[RT_DBG_SAMPLES][8];
+#endif
 
 __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 y, double par) {
   RtVec7 d;
   rt_haselgrove_3d(*E, y.v, par, d.v);
+#ifdef RT_DEV
   bool fin_in = true, fin_out = true;
 #pragma unroll
   for (int c = 0; c < 7; c++) {
@@ -134,13 +137,16 @@ __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 
   else if (!fin_in) atomicAdd(&rt_dbg_fallback[2], 1ULL);
   else if (!fin_out) atomicAdd(&rt_dbg_fallback[3], 1ULL);
   else atomicAdd(&rt_dbg_fallback[4], 1ULL);
+#endif
   return d;
 }
 template <int PRESET>
 __device__ __noinline__ RtVec4x rt_haselgrove_2d_exact(const RtDevEnv *E, RtVec4x y) {
   RtVec4x d;
   rt_haselgrove_2d<PRESET>(*E, y.v, d.v, &d.ex);
+#ifdef RT_DEV
   atomicAdd(&rt_dbg_fallback[5], 1ULL);
+#endif
   return d;
 }
 

@@ -14,10 +14,24 @@
 #include <vector>
 
 #include "rt_integrate.cuh"
+#ifdef RT_DEV
+#include "../../include/raytrace_b200_dev.h"
+#endif
 
 #define RT_VERSION_NUM 100
 
 static thread_local std::string g_last_error;
+
+// Developer switches (scheduling experiments, timelines): environment variables, read ONLY by the -DRT_DEV build
+// (libraytrace_b200_dev.so, what the diagnostics tests and profiles/ use).  The product library reads no environment
+// variable: every switch is its measured default.
+#ifdef RT_DEV
+static long long dev_env(const char *name, long long dflt) { const char *v = getenv(name); return v ? atoll(v) : dflt; }
+static bool dev_flag(const char *name) { return getenv(name) != nullptr; }
+#else
+static inline long long dev_env(const char *, long long dflt) { return dflt; }
+static inline bool dev_flag(const char *) { return false; }
+#endif
 
 #define RT_LATE_CAP 65536  // rays that may still be running when the early result copy starts
 
@@ -798,15 +812,10 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   cudaStream_t st = ctx->stream;
   // stage derivatives k[7][DIM][thread] and, when trajectories are saved, RT_STAGE staged rows per thread
   const size_t smem = (size_t)(7 * DIM + (O.save_mode ? RT_STAGE * NCOL : 0)) * RT_BLOCK * sizeof(double);
-  // the long rays' one-thread-per-ray launches may ask for more shared memory than they use, so that an SM hosting one
-  // of their blocks takes fewer bulk blocks beside it (see the chain loop)
-  static const long long prio_smem_kb = getenv("RT_PRIO_SMEM_KB") ? atoll(getenv("RT_PRIO_SMEM_KB")) : 0;
-  static const long long prio_smem_rays = getenv("RT_PRIO_SMEM_RAYS") ? atoll(getenv("RT_PRIO_SMEM_RAYS")) : 19000;
-  const size_t smem_prio = (size_t)prio_smem_kb * 1024 > smem ? (size_t)prio_smem_kb * 1024 : smem;
   // (kernel variants: one thread / 3 lanes per ray, without / with trajectory staging)
   auto k1 = O.save_mode ? rt_integrate_kernel<MODE, false, true> : rt_integrate_kernel<MODE, false, false>;
   auto k3 = O.save_mode ? rt_integrate_kernel<MODE, true, true> : rt_integrate_kernel<MODE, true, false>;
-  RT_CUDA(ctx, cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_prio));
+  RT_CUDA(ctx, cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   RT_CUDA(ctx, cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
@@ -844,7 +853,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
     int att;            // attempts per launch of the next batch (adaptive, see below)
     long long nominal;  // attempts enqueued so far (diagnostics)
   } ch[4];
-  static const long long split_min = getenv("RT_SPLIT_MIN") ? atoll(getenv("RT_SPLIT_MIN")) : 32768;
+  static const long long split_min = dev_env("RT_SPLIT_MIN", 32768);
   {
     cudaStream_t streams[4] = {st, ctx->prio_stream, ctx->aux_stream[0], ctx->aux_stream[1]};
     int *h_init = ctx->h_count + 8;  // first counters of the four chains, uploaded below when a list is cut
@@ -877,17 +886,17 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   ctx->stats.prio_rays = ch[1].upper + ch[3].upper;
   for (int c = 1; c < 4; c++)
     if (ch[c].upper > 0) RT_CUDA(ctx, cudaStreamWaitEvent(ch[c].st, ctx->ev_fork, 0));
-  const bool dbg = getenv("RT_DEBUG") != nullptr;
+  const bool dbg = dev_flag("RT_DEBUG");
   const int order[4] = {1, 3, 0, 2};  // priority chains first
   // Early result copy (host-pointer entry points with pinned result arrays, large lists): once few rays are left,
   // each chain — at its next batch boundary — saves its live list and records an event; after the four events the
   // copy stream sends every result array to the caller while the long rays go on; their records are gathered and
   // patched in after the end (solve_common).  Rays finished before a chain's event are final in memory by then.
-  const long long early_min = getenv("RT_EARLY_MIN") ? atoll(getenv("RT_EARLY_MIN")) : 262144;
+  const long long early_min = dev_env("RT_EARLY_MIN", 262144);
   const bool early = ctx->early_host != nullptr && n >= early_min;
   // (late rays are patched in by a host scatter of 14 cache lines each, 0.13 us per ray: the snapshot waits until
   // n / 512 rays are left — 2 ms before the end of cfg3, enough for its 92 MB)
-  static const long long early_div = getenv("RT_EARLY_DIV") ? atoll(getenv("RT_EARLY_DIV")) : 512;
+  static const long long early_div = dev_env("RT_EARLY_DIV", 512);
   const long long early_thr = (n / early_div < 1024) ? 1024 : ((n / early_div > RT_LATE_CAP) ? RT_LATE_CAP : n / early_div);
   bool early_trigger = false, snap[4] = {false, false, false, false};
   int nsnap = 0;
@@ -905,8 +914,6 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
           const long long before = C.upper;
           C.upper = *C.h;
           if (adapt) C.att = (C.upper * 100 >= before * 97) ? (C.att * 2 > 64 ? 64 : C.att * 2) : attempts;
-          static const int dieoff_att = getenv("RT_DIEOFF_ATT") ? atoi(getenv("RT_DIEOFF_ATT")) : 0;
-          if (adapt && dieoff_att > 0 && C.upper * 100 < before * 90) C.att = dieoff_att;
           if (dbg) {
             float ms = 0;
             cudaEventRecord(ctx->ev[2], C.st);
@@ -950,20 +957,16 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
         // chains together leave SMs idle (<= 35 k rays, i.e. 270 of the 444 resident blocks).
         // RT_COOP_POLICY=0 (developer switch) drops the second condition.
         const long long all = ch[0].upper + ch[1].upper + ch[2].upper + ch[3].upper;
-        static const int policy = getenv("RT_COOP_POLICY") ? atoi(getenv("RT_COOP_POLICY")) : 1;
-        static const long long coop_sum = getenv("RT_COOP_SUM") ? atoll(getenv("RT_COOP_SUM")) : 25000;
-        // developer switch: the priority chains also go cooperative while their attempt count is inside a window
-        static const long long win_lo = getenv("RT_COOP_WIN_LO") ? atoll(getenv("RT_COOP_WIN_LO")) : 0;
-        static const long long win_hi = getenv("RT_COOP_WIN_HI") ? atoll(getenv("RT_COOP_WIN_HI")) : 0;
-        const bool in_window = (c & 1) && C.nominal >= win_lo && C.nominal < win_hi;
-        const bool coop = C.upper <= coop_threshold && (policy == 0 || in_window || all <= coop_threshold + coop_sum);
+        static const int policy = (int)dev_env("RT_COOP_POLICY", 1);
+        static const long long coop_sum = dev_env("RT_COOP_SUM", 25000);
+        const bool coop = C.upper <= coop_threshold && (policy == 0 || all <= coop_threshold + coop_sum);
         // a launch of the priority chain has to wait for blocks of the other chain to retire before it gets SM
         // slots (stream priority does not preempt), so its slices are long: fewer waits per attempt
-        static const int coop_att = getenv("RT_COOP_ATT") ? atoi(getenv("RT_COOP_ATT")) : 32;
+        static const int coop_att = (int)dev_env("RT_COOP_ATT", 32);
         const int att = coop ? (C.att > coop_att ? C.att : coop_att) : C.att;
         // a short list still on one thread per ray is waiting for the other chains to drain: keep its batches short
         // (<= 64 attempts) so that the switch to 3 lanes per ray is not delayed by a batch already enqueued
-        static const int wait_att = getenv("RT_WAIT_ATT") ? atoi(getenv("RT_WAIT_ATT")) : 64;
+        static const int wait_att = (int)dev_env("RT_WAIT_ATT", 64);
         const int batch = coop ? 4 : ((C.upper <= coop_threshold && att * 8 > wait_att) ? (wait_att / att > 1 ? wait_att / att : 1) : 8);
         C.nominal += (long long)att * batch;
         for (int b = 0; b < batch; b++, C.k++) {
@@ -973,8 +976,7 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           else
-            k1<<<grid_for(C.upper, RT_BLOCK), RT_BLOCK,
-                 ((c & 1) && ch[1].upper + ch[3].upper <= prio_smem_rays) ? smem_prio : smem, C.st>>>(
+            k1<<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           C.cur ^= 1;
@@ -1467,6 +1469,7 @@ extern "C" int rt_traj_derived(rt_ctx *ctx, const int64_t *offsets, double *out)
   return RT_OK;
 }
 
+#ifdef RT_DEV
 // census of exact-path fallbacks since the last reset (diagnostics)
 extern "C" int rt_debug_fallback_counts(rt_ctx *ctx, unsigned long long *out8, int reset) {
   if (!ctx || !out8) return set_err(ctx, RT_ERR_INVALID, "rt_debug_fallback_counts: null argument");
@@ -1531,6 +1534,8 @@ extern "C" int rt_debug_fallback_samples(rt_ctx *ctx, double *out, int max_rows)
   RT_CUDA(ctx, cudaMemcpyFromSymbol(out, rt_dbg_sample, (size_t)rows * 8 * sizeof(double)));
   return rows;
 }
+
+#endif  // RT_DEV
 
 // ---------------------------------------------------------------------------------------------------
 // FP64 roofline denominator: NCH independent DFMA chains per thread, every SM full.  Several shapes are timed and the

@@ -3,7 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#include "../../include/raytrace_b200.h"
+#include "../../include/raytrace_b200_dev.h"
 #include "rt_fast.cuh"
 
 __device__ __forceinline__ uint64_t sm64(uint64_t &s) {

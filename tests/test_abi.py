@@ -128,3 +128,26 @@ def test_block_cyclic_partition_mirror_and_multi_create_without_gpu(have_gpu):
         assert lib.rt_multi_create(C.byref(m), C.c_int(2), None) == -2 and not m.value  # RT_ERR_NO_DEVICE
         with pytest.raises(RuntimeError, match="no CPU fallback"):
             R.MultiRayTracer("ray3d", devices=[0, 1])
+
+
+def test_product_library_exports_only_the_reference_facing_surface():
+    """libraytrace_b200.so = include/raytrace_b200.h exactly; the diagnostics of include/raytrace_b200_dev.h exist in the
+    -DRT_DEV build only; the product binary carries none of the RT_* switch names."""
+    import subprocess
+    from raytrace_b200 import build as B
+
+    def exported(path):
+        out = subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True, check=True).stdout
+        return {ln.split()[-1] for ln in out.splitlines() if " T " in ln and ln.split()[-1].startswith("rt_")}
+
+    dev_src = open(os.path.join(ROOT, "include", "raytrace_b200_dev.h")).read()
+    dev_names = set(re.findall(r"RT_API\s+[\w\s\*]+?\b(rt_\w+)\s*\(", dev_src))
+    assert len(dev_names) == 5
+    prod, dev = exported(B.LIB), exported(B.LIB_DEV)
+    assert prod == set(declared_symbols()), prod ^ set(declared_symbols())
+    assert dev == prod | dev_names
+    # (the statically linked CUDA runtime imports getenv for its own CUDA_* variables; the library's own switch names
+    # are what must be absent)
+    blob = open(B.LIB, "rb").read()
+    assert b"RT_COOP_POLICY" not in blob and b"RT_EARLY_MIN" not in blob
+    assert b"RT_COOP_POLICY" in open(B.LIB_DEV, "rb").read()

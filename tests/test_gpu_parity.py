@@ -177,7 +177,7 @@ def test_branch_free_primitives_bit_equal_exact_ones():
     """rt_fast.cuh against IEEE division / sqrt and rt_math.h on pseudo-random operands, on the device."""
     import ctypes as C
     cnt = (C.c_ulonglong * 30)()
-    assert R.api._lib().rt_selftest_fastmath(0, C.c_longlong(200), C.c_ulonglong(2024), cnt, 30) == 0
+    assert R.api._dev_lib().rt_selftest_fastmath(0, C.c_longlong(200), C.c_ulonglong(2024), cnt, 30) == 0
     for k in range(10):
         compared, mism, flagged = cnt[3 * k], cnt[3 * k + 1], cnt[3 * k + 2]
         assert compared > 5_000_000 and mism == 0, (k, compared, mism, flagged)
@@ -199,7 +199,7 @@ def test_branch_free_rhs_vouches_only_for_exact_bits_on_wild_states():
     u[100:200, 0] = np.inf
     u[200:300, 5] = 0.0
     f = rng.choice([1000.0, 5000.0, 25000.0], n)
-    rt = R.RayTracer("ray3d")
+    rt = R.RayTracer("ray3d", dev=True)  # diagnostics entry point: developer build of the library
     df, ok, de = rt.debug_rhs3d(u, f)
     rt.close()
     nan_e = np.isnan(de).all(axis=1)
@@ -316,10 +316,10 @@ def test_early_result_copy_into_pinned_arrays_matches_the_plain_copy(monkeypatch
     import torch
     launch = sweeps.sweep_3d(12, 3, 24)
     n = launch.shape[1]
-    rt = R.RayTracer("ray3d")
+    monkeypatch.setenv("RT_EARLY_MIN", "0")  # read by the developer build only, at its first solve
+    rt = R.RayTracer("ray3d", dev=True)
     rt.set_solver(maxiters=600, r_esc=10 * RE, coop_threshold=64)
     plain = rt.solve(launch)  # pageable numpy arrays: one copy at the end
-    monkeypatch.setenv("RT_EARLY_MIN", "0")
     res = R.api.SolveResult(n, 7)
     keep = []
     for name in ("u_end", "t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
@@ -331,7 +331,7 @@ def test_early_result_copy_into_pinned_arrays_matches_the_plain_copy(monkeypatch
     lp = torch.from_numpy(np.ascontiguousarray(launch)).pin_memory()
     cols = [C.c_void_p(lp[k].data_ptr()) for k in range(9)]
     for _ in range(2):
-        assert R.api._lib().rt_solve_3d(rt._ctx, C.c_int64(n), *cols, C.byref(cres)) == 0
+        assert R.api._dev_lib().rt_solve_3d(rt._ctx, C.c_int64(n), *cols, C.byref(cres)) == 0
         for k in ("u_end", "t_end", "group_delay", "status", "naccept", "nreject", "nfe", "nreflect"):
             assert _same(getattr(res, k), getattr(plain, k)), k
     assert (plain.naccept + plain.nreject).max() == 600  # long rays were still running at the snapshot
@@ -437,11 +437,17 @@ def test_cfg3_full_size_properties_and_partition():
     import ctypes as C
     full = sweeps.sweep_3d()
     n = full.shape[1]
+    rtd = R.RayTracer("ray3d", dev=True)  # the developer build keeps the census of exact-path calls
+    rtd.set_solver(r_esc=10 * RE)
+    fb = (C.c_ulonglong * 8)()
+    R.api._dev_lib().rt_debug_fallback_counts(rtd._ctx, fb, 1)
+    resd = rtd.solve(full)
+    R.api._dev_lib().rt_debug_fallback_counts(rtd._ctx, fb, 1)
+    rtd.close()
     rt = R.RayTracer("ray3d")
     rt.set_solver(r_esc=10 * RE)
     res = rt.solve(full)
-    fb = (C.c_ulonglong * 8)()
-    R.api._lib().rt_debug_fallback_counts(rt._ctx, fb, 1)
+    assert _same(res.u_end, resd.u_end) and _same(res.t_end, resd.t_end)  # product and developer builds agree
     assert set(np.unique(res.status)) == {2}  # every ray of this sweep ends on the Earth
     assert int(res.nfe.astype(np.int64).sum()) == 301445828  # the workload bench.py quotes (the oracle run over the full list gives the same)
     assert np.array_equal(res.nfe, 6 * (res.naccept + res.nreject) + 2)

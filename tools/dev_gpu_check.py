@@ -12,7 +12,7 @@ RE = 6.3712e6
 
 
 def run(name, preset, launch, **kw):
-    rt = R.RayTracer(preset)
+    rt = R.RayTracer(preset, dev=True)  # developer build: environment switches and the exact-path census
     rt.set_solver(**kw)
     for rep in range(2):
         t = time.time()
@@ -25,7 +25,7 @@ def run(name, preset, launch, **kw):
               flush=True)
     import ctypes as C
     fb = (C.c_ulonglong * 8)()
-    R.api._lib().rt_debug_fallback_counts(rt._ctx, fb, 1)
+    R.api._dev_lib().rt_debug_fallback_counts(rt._ctx, fb, 1)
     print("   exact-path fallbacks:", list(fb), "of", nfe * 2, "RHS evaluations (2 reps)", flush=True)
     u, c = np.unique(res.status, return_counts=True)
     print("   status:", {R.STATUS_NAMES[int(a)]: int(b) for a, b in zip(u, c)}, "naccept min/med/max",

@@ -2,6 +2,7 @@
 # developer tool: bench.py (cfg3) under a list of environment settings, one line of results each
 # usage: tools/gpu_env_matrix.sh "A=1 B=2" "A=3" ...   ("-" = defaults)
 mkdir -p gpurun_out
+export RT_LIB=/root/repo/ray-trace_b200/libraytrace_b200_dev.so   # the environment switches exist in the developer build only
 i=0
 for setting in "$@"; do
   i=$((i+1))
