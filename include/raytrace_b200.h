@@ -73,6 +73,13 @@ typedef struct rt_env_params {
    * FP64 can resolve (radians / metres, e.g. 1e-6 / 10): physically meaningful gradients, never bit-comparable with the
    * reference; the integrate kernel then runs its exact right-hand side (7 refractive indices instead of 5) */
   double fd_step_angle, fd_step_r;
+  /* [EXT] the physically-correct option set (TODOs at RayMain.jl:97-107, RayTrace_3D.jl:22-27,
+   * "abs() is not physical" at RayTrace_lat.jl:157,174).  Never on the parity path; LAT2D and RAY3D presets only.
+   * deriv_mode: 0 = central differences (the steps above), 1 = d(mu)/dr and d(mu)/d(theta|lambda) analytically (forward-
+   *   mode differentiation of the refractive-index code: no step, no cancellation); d(mu)/df stays the 1e-5 difference.
+   * root_mode: 0 = mu = sqrt(abs(mu^2_+)) and the d(mu)/d(psi) formula as written; 1 = the propagating root without abs
+   *   (mu^2_+ if positive, else mu^2_- if positive, else NaN) with the correct quotient rule for d(mu)/d(psi). */
+  int32_t deriv_mode, root_mode;
 } rt_env_params;
 
 /* Solver options: the keyword arguments of solve(), RayTrace_lat.jl:338 / RayTrace_3D.jl:395. */

@@ -23,6 +23,7 @@ mutable struct EnvParams      # rt_env_params
     Lppi::Float64; Lppo::Float64; ne_Lppi::Float64; ca_coef::Float64; ca_trough::Float64
     iono_n0::Float64; iono_k::Float64; iono_h::Float64
     fd_step_angle::Float64; fd_step_r::Float64   # 0 = the reference's 1e-11 (parity path)
+    deriv_mode::Int32; root_mode::Int32          # [EXT] 1 = analytic d(mu)/dr, d(mu)/dtheta; 1 = root without abs()
     EnvParams() = new()
 end
 

@@ -35,7 +35,7 @@ class EnvParams(C.Structure):
         (k, C.c_double)
         for k in ("c", "re", "B0", "e", "me", "mp", "eps", "Lppi", "Lppo", "ne_Lppi", "ca_coef", "ca_trough", "iono_n0",
                   "iono_k", "iono_h", "fd_step_angle", "fd_step_r")
-    ]
+    ] + [("deriv_mode", C.c_int32), ("root_mode", C.c_int32)]
 
 
 class SolverOpts(C.Structure):

@@ -18,6 +18,7 @@
 //     round trip; the host reads the counter once per batch of slices to shrink the grid and detect the end.
 #pragma once
 #include "rt_physics_fast.cuh"
+#include "rt_physics_ad.cuh"
 
 #ifndef RT_BLOCK
 #define RT_BLOCK 128
@@ -117,7 +118,8 @@ __device__ double rt_dbg_sample[RT_DBG_SAMPLES][8];
 
 __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 y, double par) {
   RtVec7 d;
-  rt_haselgrove_3d(*E, y.v, par, d.v);
+  if (E->deriv_mode | E->root_mode) rt_haselgrove_3d_ext(*E, y.v, par, d.v);  // [EXT] options, rt_physics_ad.cuh
+  else rt_haselgrove_3d(*E, y.v, par, d.v);
 #ifdef RT_DEV
   bool fin_in = true, fin_out = true;
 #pragma unroll
@@ -143,7 +145,8 @@ __device__ __noinline__ RtVec7 rt_haselgrove_3d_exact(const RtDevEnv *E, RtVec7 
 template <int PRESET>
 __device__ __noinline__ RtVec4x rt_haselgrove_2d_exact(const RtDevEnv *E, RtVec4x y) {
   RtVec4x d;
-  rt_haselgrove_2d<PRESET>(*E, y.v, d.v, &d.ex);
+  if (PRESET == RT_PRESET_LAT2D && (E->deriv_mode | E->root_mode)) rt_haselgrove_2d_lat_ext(*E, y.v, d.v, &d.ex);
+  else rt_haselgrove_2d<PRESET>(*E, y.v, d.v, &d.ex);
 #ifdef RT_DEV
   atomicAdd(&rt_dbg_fallback[5], 1ULL);
 #endif
@@ -255,6 +258,12 @@ __device__ __noinline__ double rt_pow_dev(double x, double p) { return rt_pow_po
 // save_func at an event point (the only sample that is not a stage point), out of line
 template <int PRESET>
 __device__ __noinline__ void rt_extras_at(const RtDevEnv &E, const double *u, RtExtras2D *ex) {
+  if (PRESET == RT_PRESET_LAT2D && E.root_mode) {
+    RtMuAD o;
+    rd_mu2d_lat(E, u[0], u[1], u[2], u[3], o);
+    *ex = RtExtras2D{o.mu.v, o.dmudpsi, o.dip, o.psi};
+    return;
+  }
   RtMu m = rt_phase_refractive_index_2d<PRESET>(E, u[0], u[1], u[2], u[3], &ex->dip, &ex->psi);
   ex->mu = m.mu;
   ex->dmudpsi = m.dmudpsi;

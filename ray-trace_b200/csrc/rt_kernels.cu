@@ -266,7 +266,10 @@ static void make_dev_env(const rt_env_params &e, RtDevEnv &d) {
   d.density_model = e.density_model;
   d.h_ang = e.fd_step_angle > 0.0 ? e.fd_step_angle : 1.0e-11;
   d.h_r = e.fd_step_r > 0.0 ? e.fd_step_r : 1.0e-11;
-  d.fd_default = !(e.fd_step_angle > 0.0) && !(e.fd_step_r > 0.0);
+  d.deriv_mode = e.deriv_mode;
+  d.root_mode = e.root_mode;
+  // the branch-free right-hand side covers the files' own arithmetic only
+  d.fd_default = !(e.fd_step_angle > 0.0) && !(e.fd_step_r > 0.0) && e.deriv_mode == 0 && e.root_mode == 0;
 }
 
 static int refresh_rcp(rt_ctx *ctx) {
@@ -426,6 +429,10 @@ extern "C" int rt_set_env(rt_ctx *ctx, const rt_env_params *env) {
     return set_err(ctx, RT_ERR_INVALID, "rt_set_env: bad density_model %d", env->density_model);
   if (!(env->fd_step_angle >= 0.0) || !(env->fd_step_r >= 0.0))
     return set_err(ctx, RT_ERR_INVALID, "rt_set_env: finite-difference steps must be >= 0 (0 = the reference's 1e-11)");
+  if (env->deriv_mode < 0 || env->deriv_mode > 1 || env->root_mode < 0 || env->root_mode > 1)
+    return set_err(ctx, RT_ERR_INVALID, "rt_set_env: deriv_mode and root_mode must be 0 or 1");
+  if ((env->deriv_mode || env->root_mode) && env->preset != RT_PRESET_LAT2D && env->preset != RT_PRESET_RAY3D)
+    return set_err(ctx, RT_ERR_INVALID, "rt_set_env: deriv_mode / root_mode are implemented for the LAT2D and RAY3D presets");
   ctx->env = *env;
   make_dev_env(ctx->env, ctx->denv);
   return refresh_rcp(ctx);
@@ -481,6 +488,13 @@ __global__ void rt_mu2d_kernel(const __grid_constant__ RtDevEnv E, long long n, 
                                const double *f, double *mu, double *dmu) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  if (MODE == RT_PRESET_LAT2D && E.root_mode) {  // [EXT] root selection without abs (rt_physics_ad.cuh)
+    RtMuAD o;
+    rd_mu2d_lat(E, r[i], th[i], chi[i], f[i], o);
+    mu[i] = o.mu.v;
+    dmu[i] = o.dmudpsi;
+    return;
+  }
   RtMu m = rt_phase_refractive_index_2d<MODE>(E, r[i], th[i], chi[i], f[i], nullptr, nullptr);
   mu[i] = m.mu;
   dmu[i] = m.dmudpsi;
@@ -492,6 +506,12 @@ __global__ void rt_mu3d_kernel(const __grid_constant__ RtDevEnv E, long long n, 
   RtGeo3D g;
   rt_geo3d(E, in[i], in[n + i], in[3 * n + i], in[4 * n + i], in[5 * n + i], g);
   RtMu m = rt_stix(g.p, (2.0 * RT_PI) * in[6 * n + i], true);
+  if (E.root_mode) {  // [EXT] root selection without abs (rt_physics_ad.cuh)
+    RtMuAD o;
+    rd_mu3d(E, in[i], in[n + i], in[3 * n + i], in[4 * n + i], in[5 * n + i], in[6 * n + i], o);
+    m.mu = o.mu.v;
+    m.dmudpsi = o.dmudpsi;
+  }
   out[i] = m.mu;
   out[n + i] = m.dmudpsi;
   out[2 * n + i] = g.psi;

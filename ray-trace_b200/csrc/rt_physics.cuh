@@ -35,6 +35,7 @@ struct RtDevEnv {
   int density_model;  // rt_env_params.density_model
   int fd_default;     // 1: both finite-difference steps are the files' 1.0e-11 (the branch-free path's precondition)
   double h_ang, h_r;  // finite-difference steps of d(mu)/d(theta|lambda), d(mu)/dr (rt_env_params.fd_step_*)
+  int deriv_mode, root_mode;  // rt_env_params: [EXT] analytic partials / root selection without abs (rt_physics_ad.cuh)
 };
 
 struct RtPlasma {  // local medium at one point (independent of wave frequency)

@@ -28,7 +28,7 @@ def test_every_declared_symbol_is_exported():
 
 
 def test_struct_layouts_match_header():
-    assert C.sizeof(R.EnvParams) == 8 + 17 * 8
+    assert C.sizeof(R.EnvParams) == 8 + 17 * 8 + 8
     assert C.sizeof(R.SolverOpts) == 4 * 4 + 8 + 7 * 8 + 16
     assert C.sizeof(R.SolverOpts) == C.sizeof(O.SolverOpts)
 

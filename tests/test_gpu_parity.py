@@ -607,3 +607,71 @@ def test_trajectory_pack_on_the_device_and_bad_capacity():
     with pytest.raises(RuntimeError, match="max_samples >= 2"):
         rt.set_solver(save_mode=1, max_samples=1)
     rt.close()
+
+
+def test_analytic_partials_and_root_selection_options():
+    """SURVEY §8 f4, off the parity path.  deriv_mode = 1: d(mu)/dr and d(mu)/d(theta) by forward-mode differentiation
+    agree with central differences at steps FP64 can resolve (fd_step_angle = 1e-6 rad, fd_step_r = 10 m) to 1e-6
+    relative, and leave the components that do not use them untouched.  root_mode = 1: the propagating root without
+    abs() — equal to the as-written mu wherever mu^2_+ > 0, sqrt(mu^2_-) or NaN elsewhere."""
+    import tools_golden as TG
+    r, th, ph, rho, f = _points_3d(800, 41)
+    u = np.vstack([r, th, ph, rho, np.zeros_like(r)])
+    e_fd = R.env_preset("ray3d")
+    e_fd.fd_step_angle, e_fd.fd_step_r = 1e-6, 10.0
+    e_ad = R.env_preset("ray3d")
+    e_ad.deriv_mode = 1
+    rt_fd, rt_ad = R.RayTracer("ray3d", env=e_fd), R.RayTracer("ray3d", env=e_ad)
+    d_fd, d_ad = rt_fd.haselgrove(u, [f]), rt_ad.haselgrove(u, [f])
+    for k in (0, 1, 2, 5, 6):
+        assert np.allclose(d_ad[k], d_fd[k], rtol=1e-12, atol=0.0), k  # no r / theta partial in these
+    scale = np.abs(d_fd[4]) + np.abs(rho[1] * d_fd[0]) / r
+    assert np.max(np.abs(d_ad[4] - d_fd[4]) / scale) < 1e-6                      # (1/mu) d(mu)/d(theta) term
+    scale3 = np.abs(d_fd[3]) + np.abs(rho[1] * d_fd[1])
+    assert np.max(np.abs(d_ad[3] - d_fd[3]) / scale3) < 1e-6                     # (1/mu) d(mu)/dr term
+    d0 = R.RayTracer("ray3d").haselgrove(u, [f])
+    assert not np.allclose(d_ad[3], d0[3], rtol=1e-3)                            # as written that term is exactly 0
+    launch = sweeps.sweep_3d(3, 2, 6)
+    for coop in (-1, 10 ** 9):
+        rt_ad.set_solver(maxiters=400, r_esc=10 * RE, coop_threshold=coop)
+        rt_fd.set_solver(maxiters=400, r_esc=10 * RE, coop_threshold=coop)
+        a, b = rt_ad.solve(launch), rt_fd.solve(launch)
+        assert np.array_equal(a.status, b.status) and np.allclose(a.t_end, b.t_end, rtol=2e-2)
+    rt_fd.close()
+    rt_ad.close()
+    # 2D
+    r, lam, chi, f = _points_2d(800, 42)
+    u2 = np.vstack([r, lam, chi, f])
+    e_fd, e_ad = R.env_preset("lat2d"), R.env_preset("lat2d")
+    e_fd.fd_step_angle, e_fd.fd_step_r = 1e-6, 10.0
+    e_ad.deriv_mode = 1
+    a, b = R.RayTracer("lat2d", env=e_ad).haselgrove(u2), R.RayTracer("lat2d", env=e_fd).haselgrove(u2)
+    assert np.allclose(a[[0, 1, 3]], b[[0, 1, 3]], rtol=1e-12, atol=0.0)
+    assert np.max(np.abs(a[2] - b[2]) / (np.abs(b[2]) + np.abs(b[1]))) < 1e-6
+    # root selection
+    e_rt = R.env_preset("lat2d")
+    e_rt.root_mode = 1
+    rt_rt = R.RayTracer("lat2d", env=e_rt)
+    mu1, dmu1 = rt_rt.phase_refractive_index(r, lam, chi, f)
+    mu0, _ = R.RayTracer("lat2d").phase_refractive_index(r, lam, chi, f)
+    ref = [TG.pri_lat(*p) for p in zip(r, lam, chi, f)]
+    m2p = np.array([q["mu2_plus"] for q in ref])
+    m2m = np.array([(q["B"] - q["F"]) / (2 * q["A"]) for q in ref])
+    pos = m2p > 0
+    assert 0.05 < pos.mean() < 0.95                      # both cases occur in the sample
+    assert np.allclose(mu1[pos], mu0[pos], rtol=1e-13)
+    neg = ~pos & (m2m > 0)
+    assert neg.any() and np.allclose(mu1[neg], np.sqrt(m2m[neg]), rtol=1e-9)
+    assert np.isnan(mu1[~pos & ~(m2m > 0)]).all()
+    # the corrected d(mu)/d(psi) is the derivative of the selected root: check against a psi difference of mu itself
+    h = 1e-6
+    mu_p, _ = rt_rt.phase_refractive_index(r, lam, chi + h / 2, f)
+    mu_m, _ = rt_rt.phase_refractive_index(r, lam, chi - h / 2, f)
+    ok = np.isfinite(mu1) & np.isfinite(mu_p) & np.isfinite(mu_m)
+    num = (mu_p - mu_m) / h                                # psi = pi/2 + dip + chi: d/dchi = d/dpsi
+    assert np.max(np.abs(dmu1[ok] - num[ok]) / (np.abs(num[ok]) + 1e-3 * mu1[ok])) < 1e-5
+    rt_rt.close()
+    bad = R.env_preset("raymain")
+    bad.deriv_mode = 1
+    with pytest.raises(RuntimeError, match="LAT2D and RAY3D"):
+        R.RayTracer("raymain", env=bad)
