@@ -166,20 +166,23 @@ RT_HD double rt_scale2(double y, int k) {
 /* ---------------------------------------------------------------- exp ---- */
 /* exp(r) on |r| <= 0.35 as 1 + r + r^2 q(r), q = Taylor to r^11 (truncation < 2^-57) */
 RT_HD double rt_exp_kernel(double r, double tail) {
-  double q = RT_CK(EXP0);
-  q = RT_FMA(q, r, RT_CK(EXP1));
-  q = RT_FMA(q, r, RT_CK(EXP2));
-  q = RT_FMA(q, r, RT_CK(EXP3));
-  q = RT_FMA(q, r, RT_CK(EXP4));
-  q = RT_FMA(q, r, RT_CK(EXP5));
-  q = RT_FMA(q, r, RT_CK(EXP6));
-  q = RT_FMA(q, r, RT_CK(EXP7));
-  q = RT_FMA(q, r, RT_CK(EXP8));
-  q = RT_FMA(q, r, RT_CK(EXP9));
-  q = RT_FMA(q, r, RT_CK(EXP10));
-  q = RT_FMA(q, r, 0.5);
-  double r2 = r * r;
-  double lo = RT_FMA(r2, q, tail);
+  /* q(r) = EXP0 r^11 + ... + EXP10 r + 1/2 as two interleaved Horner chains in z = r^2 (even and odd powers): half the
+   * dependent depth of one chain in r */
+  double z = r * r;
+  double qo = RT_CK(EXP0);
+  double qe = RT_CK(EXP1);
+  qo = RT_FMA(qo, z, RT_CK(EXP2));
+  qe = RT_FMA(qe, z, RT_CK(EXP3));
+  qo = RT_FMA(qo, z, RT_CK(EXP4));
+  qe = RT_FMA(qe, z, RT_CK(EXP5));
+  qo = RT_FMA(qo, z, RT_CK(EXP6));
+  qe = RT_FMA(qe, z, RT_CK(EXP7));
+  qo = RT_FMA(qo, z, RT_CK(EXP8));
+  qe = RT_FMA(qe, z, RT_CK(EXP9));
+  qo = RT_FMA(qo, z, RT_CK(EXP10));
+  qe = RT_FMA(qe, z, 0.5);
+  double q = RT_FMA(qo, r, qe);
+  double lo = RT_FMA(z, q, tail);
   return 1.0 + (r + lo);
 }
 

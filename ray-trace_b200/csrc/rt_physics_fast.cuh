@@ -126,7 +126,7 @@ RTF RtMu rtf_stix(const RtPlasma &p, double omega, bool &ok) {
   if (WITH_D) {
     const double dA = ((2.0 * (S - P)) * s) * c;
     const double dB = ((2.0 * X) * s) * c;
-    const double dF = rtf_div(1.0, 2.0 * F, ok) * ((((X * X) * 4.0) * (s2 * s)) * c - ((8.0 * (PD * PD)) * s) * c);
+    const double dF = rtf_inv(2.0 * F, ok) * ((((X * X) * 4.0) * (s2 * s)) * c - ((8.0 * (PD * PD)) * s) * c);
     bool ok1 = true;
     double t1 = rtf_div_y(dB + dF, A2, yA, ok1);
     const bool z1 = (dB + dF) == 0.0;  // psi = 0, pi/2, pi: the reference's own check values (scratch.jl:212-220)
@@ -138,7 +138,7 @@ RTF RtMu rtf_stix(const RtPlasma &p, double omega, bool &ok) {
     const bool z2 = (n2 == 0.0);
     t2 = z2 ? n2 : t2;  // divisor 2 A^2 > 0
     ok = ok && (ok2 || z2);
-    out.dmudpsi = rtf_div(1.0, 2.0 * out.mu, ok) * (t1 - t2);
+    out.dmudpsi = rtf_inv(2.0 * out.mu, ok) * (t1 - t2);
   }
   return out;
 }
@@ -206,13 +206,13 @@ RTF void rtf_tail3d(const RtDevEnv &E, const RtRad3D &Rd, const double *u, doubl
   rtf_sincos(th, &st, &ct, ok);
   const double rmm = r * mm;
   const double ymu = rtf_rcp(mu);
-  const double imu = rtf_div_y(1.0, mu, ymu, ok);
-  du[0] = rtf_div(1.0, mm, ok) * (rr_ - mu * dmr);
-  du[1] = rtf_div(1.0, rmm, ok) * (rt_ - mu * dmt);
-  du[2] = rtf_div(1.0, rmm * st, ok) * (rp_ - mu * dmp);
+  const double imu = rtf_inv_y(mu, ymu, ok);
+  du[0] = rtf_inv(mm, ok) * (rr_ - mu * dmr);
+  du[1] = rtf_inv(rmm, ok) * (rt_ - mu * dmt);
+  du[2] = rtf_inv(rmm * st, ok) * (rp_ - mu * dmp);
   du[3] = (0.0 + rt_ * du[1]) + (rp_ * du[2]) * st;  // (1/mu) d(mu)/dr = +0 (r -+ 5e-12 == r, 1/mu finite)
-  du[4] = rtf_div_y(1.0, r, Rd.yr, ok) * ((imu * dmudt - rt_ * du[0]) + ((r * rp_) * du[2]) * ct);
-  du[5] = rtf_div(1.0, r * st, ok) * ((0.0 - (rp_ * du[0]) * st) - ((r * rp_) * du[1]) * ct);  // (1/mu) d(mu)/dphi = +0
+  du[4] = rtf_inv_y(r, Rd.yr, ok) * ((imu * dmudt - rt_ * du[0]) + ((r * rp_) * du[2]) * ct);
+  du[5] = rtf_inv(r * st, ok) * ((0.0 - (rp_ * du[0]) * st) - ((r * rp_) * du[1]) * ct);  // (1/mu) d(mu)/dphi = +0
   du[6] = E.inv_c * (1.0 + rtf_div_y(freq, mu, ymu, ok) * dmudf);
 }
 
@@ -404,7 +404,7 @@ RTF bool rtf_haselgrove_2d_lat(const RtDevEnv &E, const double *u, double *du, R
   const double mu = c.mu, dmudpsi = c.dmudpsi;
   const double mm = mu * mu;
   const double rmm = r * mm;
-  const double i1 = rtf_div(1.0, mm, ok), i2 = rtf_div(1.0, rmm, ok);
+  const double i1 = rtf_inv(mm, ok), i2 = rtf_inv(rmm, ok);
   du[0] = i1 * (mu * cc + dmudpsi * sc);
   du[1] = i2 * (mu * sc - dmudpsi * cc);
   du[2] = i2 * (dmudth * cc - mu * sc);  // r d(mu)/dr + mu = +0 + mu = mu (r > 0, mu > 0)

@@ -449,7 +449,7 @@ def test_cfg3_full_size_properties_and_partition():
     res = rt.solve(full)
     assert _same(res.u_end, resd.u_end) and _same(res.t_end, resd.t_end)  # product and developer builds agree
     assert set(np.unique(res.status)) == {2}  # every ray of this sweep ends on the Earth
-    assert int(res.nfe.astype(np.int64).sum()) == 301445828  # the workload bench.py quotes (the oracle run over the full list gives the same)
+    assert int(res.nfe.astype(np.int64).sum()) == 301897484  # the workload bench.py quotes (the oracle run over the full list gives the same)
     assert np.array_equal(res.nfe, 6 * (res.naccept + res.nreject) + 2)
     assert np.max(np.abs(res.u_end[0] - RE)) < 1e-6 and np.all(res.t_end > 0)  # metres: bisection to 1 ulp in theta
     assert _same(res.group_delay, res.u_end[6])
@@ -636,7 +636,8 @@ def test_analytic_partials_and_root_selection_options():
         rt_ad.set_solver(maxiters=400, r_esc=10 * RE, coop_threshold=coop)
         rt_fd.set_solver(maxiters=400, r_esc=10 * RE, coop_threshold=coop)
         a, b = rt_ad.solve(launch), rt_fd.solve(launch)
-        assert np.array_equal(a.status, b.status) and np.allclose(a.t_end, b.t_end, rtol=2e-2)
+        down = a.status == 2  # rays that reach the ground: same path to within the solver tolerance (1e-3)
+        assert np.array_equal(a.status, b.status) and down.sum() > 10 and np.allclose(a.t_end[down], b.t_end[down], rtol=1e-2)
     rt_fd.close()
     rt_ad.close()
     # 2D
