@@ -79,8 +79,11 @@ RTF double rtf_density_cm3(const RtDevEnv &E, double ne_iono, double L, bool &ok
   // rt_exp10 returns +Inf above 308.2547...; 308.5 has a round high word (arg10 is finite or +Inf here)
   ovf = ok && seg1 && (huge || __double2hiint(arg10) >= 0x40734800);
   double p10 = rtf_exp10(arg10, ok);
+  // L^-4.5 (a sqrt and a division) is needed by the trough segment only: skipped when no lane of the converged group
+  // is there (a uniform branch; the value is unused by the other segments, so the bits do not depend on the vote)
   bool ok3 = true;
-  double pw = rtf_pow_m4p5(seg3 ? L : 1.0, ok3);
+  double pw = 1.0;
+  if (__ballot_sync(__activemask(), seg3) != 0u) pw = rtf_pow_m4p5(seg3 ? L : 1.0, ok3);
   ok = ok && (ok3 || !seg3);
   double ne_plasma = 0.0;
   ne_plasma = seg1 ? p10 : ne_plasma;
@@ -98,10 +101,9 @@ RTF void rtf_plasma_from(const RtDevEnv &E, double n_e, double Bmag, RtPlasma &p
 }
 
 // rt_stix with shared reciprocals
+// (w2 = omega omega and yw = rtf_rcp(w2) are passed in: the three theta points of one right-hand side share them)
 template <bool WITH_D>
-RTF RtMu rtf_stix(const RtPlasma &p, double omega, bool &ok) {
-  const double w2 = omega * omega;
-  const double yw = rtf_rcp(w2);
+RTF RtMu rtf_stix(const RtPlasma &p, double omega, double w2, double yw, bool &ok) {
   const double xe = rtf_div_y(p.w_e2, w2, yw, ok), xp = rtf_div_y(p.w_p2, w2, yw, ok);
   const double R = 1.0 - xe * rtf_div(omega, omega - p.W_e, ok) - xp * rtf_div(omega, omega + p.W_p, ok);
   const double L = 1.0 - xe * rtf_div(omega, omega + p.W_e, ok) - xp * rtf_div(omega, omega - p.W_p, ok);
@@ -141,6 +143,12 @@ RTF RtMu rtf_stix(const RtPlasma &p, double omega, bool &ok) {
     out.dmudpsi = rtf_inv(2.0 * out.mu, ok) * (t1 - t2);
   }
   return out;
+}
+
+template <bool WITH_D>
+RTF RtMu rtf_stix(const RtPlasma &p, double omega, bool &ok) {
+  const double w2 = omega * omega;
+  return rtf_stix<WITH_D>(p, omega, w2, rtf_rcp(w2), ok);
 }
 
 // =====================================================================================================
@@ -271,14 +279,15 @@ RTF bool rtf_haselgrove_3d(const RtDevEnv &E, const double *u, double freq, doub
   } else {
     // centre first (with d(mu)/d(psi)); the theta -/+ and f -/+ pairs are loops so that the build can choose
     // between rolled (small register footprint, more resident warps) and unrolled (more chains per warp)
+    const double om = two_pi * freq, om2 = om * om, yom2 = rtf_rcp(om2);
     rtf_geo3d(E, Rd, r, th, rr_, rt_, gc, ok, ovf_c);
-    c = rtf_stix<true>(gc.p, two_pi * freq, ok);
+    c = rtf_stix<true>(gc.p, om, om2, yom2, ok);
     double mt[2], mf[2];
     RT_PAIR_LOOP
     for (int k = 0; k < 2; k++) {
       RtGeo3D g;
       rtf_geo3d(E, Rd, r, k ? th + 1.0e-11 / 2.0 : th - 1.0e-11 / 2.0, rr_, rt_, g, ok, ovf_x);
-      const double m = rtf_stix<false>(g.p, two_pi * freq, ok).mu;
+      const double m = rtf_stix<false>(g.p, om, om2, yom2, ok).mu;
       if (k == 0) mt[0] = m; else mt[1] = m;
     }
     RT_PAIR_LOOP_F
@@ -376,15 +385,16 @@ RTF bool rtf_haselgrove_2d_lat(const RtDevEnv &E, const double *u, double *du, R
     psi = rt_group_get(psi, 0);
   } else {
     RtPlasma pc;
+    const double om = two_pi * freq, om2 = om * om, yom2 = rtf_rcp(om2);
     rtf_geo2d_lat(E, Rd, r, th, chi, pc, dip, psi, ok);
-    c = rtf_stix<true>(pc, two_pi * freq, ok);
+    c = rtf_stix<true>(pc, om, om2, yom2, ok);
     double mt[2], mf[2];
     RT_PAIR_LOOP
     for (int k = 0; k < 2; k++) {
       RtPlasma p;
       double d0, d1;
       rtf_geo2d_lat(E, Rd, r, k ? th + 1.0e-11 / 2.0 : th - 1.0e-11 / 2.0, chi, p, d0, d1, ok);
-      const double m = rtf_stix<false>(p, two_pi * freq, ok).mu;
+      const double m = rtf_stix<false>(p, om, om2, yom2, ok).mu;
       if (k == 0) mt[0] = m; else mt[1] = m;
     }
     RT_PAIR_LOOP_F
