@@ -31,6 +31,11 @@ RT_API int rt_debug_fallback_samples(rt_ctx *ctx, double *out, int max_rows);
 /* cycles per dependent operation with `warps` warps resident on one SM:
  * res[6] = DFMA, DMUL, DADD, MUFU.RCP64H chains, then 2 and 4 independent DFMA chains per thread */
 RT_API int rt_probe_latency(int device, int warps, double *res);
+/* FP64 pipe throughput of synthetic instruction streams with `warps_per_sched` warps per scheduler, as a fraction of the
+ * nominal rate (one FP64 warp instruction per 2 cycles per scheduler) at clock_mhz: res[5] = {DFMA with reused operands,
+ * DFMA with three distinct register operands, DFMA/DMUL/DADD mix, + one integer instruction per FP64 instruction,
+ * + one FP32 compare/select per FP64 instruction}; run it under ncu for sm__pipe_fp64_cycles_active */
+RT_API int rt_probe_pipe(int device, int warps_per_sched, double clock_mhz, double *res);
 
 #ifdef __cplusplus
 }

@@ -167,3 +167,78 @@ extern "C" RT_API int rt_probe_latency(int device, int warps, double *res) {
   cudaFree(out); cudaFree(cyc);
   return e == cudaSuccess ? RT_OK : RT_ERR_CUDA;
 }
+
+// ---- FP64 pipe throughput probes: what a real instruction stream can reach --------------------------------------------
+// variant 0: x_c = fma(x_c, a, b)             (the peak microbenchmark: two operands from the reuse cache)
+// variant 1: x_c = fma(x_c+1, x_c+2, x_c+3)   (three distinct register pairs per DFMA, as in real code)
+// variant 2: variant 1, alternating DFMA / DMUL / DADD
+// variant 3: variant 1 with one integer instruction (LOP3 on a side value) after every DFMA (40 % non-FP64, as the kernel)
+// variant 4: variant 1 with one FP32 compare + select after every DFMA (the guard logic of the branch-free divisions)
+// `warps_per_sched` x 4 warps per SM (blocks of 128 threads), NCH chains per thread
+template <int VAR, int NCH>
+__global__ void __launch_bounds__(128) rt_pipe_kernel(double *out, int iters, double a, double b) {
+  double x[NCH], kk[NCH];  // kk: small per-chain factors held in registers, so that the values stay bounded
+#pragma unroll
+  for (int c = 0; c < NCH; c++) {
+    x[c] = 1.0 + 1e-3 * (threadIdx.x + c);
+    kk[c] = a * 1e-12 * (c + 1);
+  }
+  unsigned side = threadIdx.x;
+  float fs = (float)threadIdx.x;
+#pragma unroll 2
+  for (int k = 0; k < iters; k++) {
+#pragma unroll
+    for (int c = 0; c < NCH; c++) {
+      if (VAR == 0) x[c] = __fma_rn(x[c], a, b);
+      else if (VAR == 2 && (c % 3) == 1) x[c] = __dmul_rn(x[(c + 1) % NCH], kk[(c + 2) % NCH]) + 0.0 * b;
+      else if (VAR == 2 && (c % 3) == 2) x[c] = __dadd_rn(x[(c + 3) % NCH], kk[(c + 1) % NCH]);
+      else x[c] = __fma_rn(x[(c + 1) % NCH], kk[(c + 2) % NCH], x[(c + 3) % NCH]);
+      if (VAR == 3) side = (side ^ (side << 1)) & 0x7fffffffu;
+      if (VAR == 4) fs = (fabsf(fs) < 6.5e-37f) ? fs + 1.0f : fs;
+    }
+  }
+  double s = (double)side + (double)fs;
+#pragma unroll
+  for (int c = 0; c < NCH; c++) s += x[c];
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// res[5] = FP64 warp instructions per cycle per scheduler x 2.0 for the five variants (1.0 = nominal pipe rate);
+// wall-clock based (CUDA events), SM clock taken as clock_mhz
+extern "C" RT_API int rt_probe_pipe(int device, int warps_per_sched, double clock_mhz, double *res) {
+  if (!res || warps_per_sched < 1 || warps_per_sched > 12) return RT_ERR_INVALID;
+  if (cudaSetDevice(device) != cudaSuccess) return RT_ERR_NO_DEVICE;
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  const int blocks = prop.multiProcessorCount * warps_per_sched, iters = 1 << 13;
+  constexpr int NCH = 8;
+  double *out;
+  cudaMalloc(&out, (size_t)blocks * 128 * sizeof(double));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  for (int v = 0; v < 5; v++) {
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; rep++) {
+      cudaEventRecord(e0);
+      if (v == 0) rt_pipe_kernel<0, NCH><<<blocks, 128>>>(out, iters, 0.9999999, 1e-7);
+      if (v == 1) rt_pipe_kernel<1, NCH><<<blocks, 128>>>(out, iters, 0.9999999, 1e-7);
+      if (v == 2) rt_pipe_kernel<2, NCH><<<blocks, 128>>>(out, iters, 0.9999999, 1e-7);
+      if (v == 3) rt_pipe_kernel<3, NCH><<<blocks, 128>>>(out, iters, 0.9999999, 1e-7);
+      if (v == 4) rt_pipe_kernel<4, NCH><<<blocks, 128>>>(out, iters, 0.9999999, 1e-7);
+      cudaEventRecord(e1);
+      cudaEventSynchronize(e1);
+      float ms;
+      cudaEventElapsedTime(&ms, e0, e1);
+      if (ms < best) best = ms;
+    }
+    const double fp64_inst = (double)warps_per_sched * iters * NCH;  // chain ops only
+    const double cycles = best * 1e-3 * clock_mhz * 1e6;
+    res[v] = 2.0 * fp64_inst / cycles;
+  }
+  cudaError_t e = cudaDeviceSynchronize();
+  cudaFree(out);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return e == cudaSuccess ? RT_OK : RT_ERR_CUDA;
+}
