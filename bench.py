@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays-per-gpu", type=int, default=0, help="override (testing only)")
     ap.add_argument("--slice", type=int, default=0)
+    ap.add_argument("--coop-threshold", type=int, default=0, help="developer: rt_solver_opts.coop_threshold (0 = default)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="rays in the CPU sample (0 = default)")
     ap.add_argument("--maxiters", type=int, default=0, help="iteration cap override (a cut-off run: named in config)")
     ap.add_argument("--skip-e2e", action="store_true",
@@ -92,6 +93,7 @@ def make_launch(workload, world, rank, rays_per_gpu=0):
 
 
 MAXITERS_OVERRIDE = 0
+COOP_THRESHOLD = 0
 
 
 def solver_kwargs(workload, slice_attempts=0):
@@ -108,6 +110,8 @@ def solver_kwargs(workload, slice_attempts=0):
         kw["maxiters"] = MAXITERS_OVERRIDE
     if slice_attempts:
         kw["slice_attempts"] = slice_attempts
+    if COOP_THRESHOLD:
+        kw["coop_threshold"] = COOP_THRESHOLD
     return kw
 
 
@@ -166,6 +170,7 @@ def cpu_oracle_run(workload, launch, nthreads):
     import oracle_lib as O
     kw = solver_kwargs(workload)
     kw.pop("adaptive")
+    kw.pop("coop_threshold", None)  # scheduling only
     o = O.opts(**kw)
     E = O.env(O.RAY3D if IS3D[workload] else O.LAT2D)
     t = time.perf_counter()
@@ -224,9 +229,10 @@ def run_reference(args, rank, world):
 
 
 def main():
-    global MAXITERS_OVERRIDE
+    global MAXITERS_OVERRIDE, COOP_THRESHOLD
     args = parse()
     MAXITERS_OVERRIDE = args.maxiters
+    COOP_THRESHOLD = args.coop_threshold
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -278,6 +284,7 @@ def main():
 
     for _ in range(args.warmup):
         step_device()
+    peak = max(peak, rt.measure_fp64_peak())  # again with the clocks up: the larger figure is the denominator
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -295,6 +302,7 @@ def main():
         slices += st.slices
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+    peak = max(peak, rt.measure_fp64_peak())
     ms_local = sum(a.elapsed_time(b) for a, b in ev)
     nfe_local = int(ints[3].to(torch.int64).sum().item())
     status_h = ints[0].cpu().numpy()
