@@ -52,6 +52,18 @@ def partition_indices(n, rank, world, layout="contiguous"):
     Rays are independent, so any partition gives the same per-ray results; strided balances sweeps whose expensive
     rays cluster in one part of the launch list (cfg3: the long magnetospheric paths sit at high colatitude)."""
     import numpy as _np
+    if layout.startswith("rootlight"):
+        # "rootlight:K" = rotated, except that in every K-th block of `world` rays the ray that would go to rank 0 goes
+        # to one of the other ranks (round robin): the gather root traces 1/K fewer rays and spends the time it saves on
+        # receiving and placing everybody's records, so that no rank waits for it
+        K = int(layout.split(":")[1])
+        i = _np.arange(n, dtype=_np.int64)
+        b = i // world
+        owner = (i % world + b) % world
+        if world > 1:
+            move = (owner == 0) & (b % K == 0)
+            owner[move] = 1 + (b[move] // K) % (world - 1)
+        return i[owner == rank]
     if layout == "strided":
         return _np.arange(rank, n, world)
     if layout == "rotated":
