@@ -42,8 +42,8 @@ SCALING = {"cfg3": "weak", "cfg2": "weak", "cfg4": "weak", "cfg5": "strong", "cf
 # 8192 rows of 72 B per ray, iteration cap 8190 so that no trajectory is truncated -> 59 GB of trajectory rows per step
 SAVE_ROWS = 8192
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-list launch of rt_integrate_kernel (4 attempts for each of
-# 10^6 rays, 7813 blocks) from the ncu --set full capture summarised in profiles/r1_ncu_integrate_v3.md:
-# 176.3 MB + 115.6 MB.  Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 10^6 = 0.4 GB upper bound.
+# 10^6 rays, 7813 blocks) from the ncu --set full capture summarised in profiles/r2_ncu_integrate.md:
+# 176.4 MB + 120.4 MB.  Algorithmic traffic of that launch: ray state in and out, 2 x ~200 B x 10^6 = 0.4 GB upper bound.
 # launch-list partition across ranks: block b of N consecutive rays goes to the ranks rotated by b, so that every GPU
 # gets its share of the long rays AND of every wave-normal angle (plain strided: +-4.5 % work per rank on 8 GPUs)
 PARTITION = "rotated"
@@ -55,7 +55,7 @@ def partition_layout(world, is3d):
     if world > 1 and is3d:
         return "rootlight:%d" % max(2, int(round(1.0 / (0.004 * world))))
     return PARTITION
-NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 291.9e6, "cfg5": None, "cfg2": 13.3e6, "cfg4": None, "cfg2save": None}
+NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 296.8e6, "cfg5": None, "cfg2": 13.3e6, "cfg4": None, "cfg2save": None}
 
 
 def parse():

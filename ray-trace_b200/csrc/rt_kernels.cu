@@ -833,9 +833,14 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   // stage derivatives k[7][DIM][thread] and, when trajectories are saved, RT_STAGE staged rows per thread
   const size_t smem = (size_t)(7 * DIM + (O.save_mode ? RT_STAGE * NCOL : 0)) * RT_BLOCK * sizeof(double);
   // (kernel variants: one thread / 3 lanes per ray, without / with trajectory staging)
+  // developer switch: the long rays' one-thread-per-ray launches ask for more shared memory than they use, so that an
+  // SM hosting one of their blocks takes one bulk block beside it instead of two (130 kB) or none (180 kB)
+  static const long long prio_smem_kb = dev_env("RT_PRIO_SMEM_KB", 0);
+  static const long long prio_smem_rays = dev_env("RT_PRIO_SMEM_RAYS", 19000);
+  const size_t smem_prio = (size_t)prio_smem_kb * 1024 > smem ? (size_t)prio_smem_kb * 1024 : smem;
   auto k1 = O.save_mode ? rt_integrate_kernel<MODE, false, true> : rt_integrate_kernel<MODE, false, false>;
   auto k3 = O.save_mode ? rt_integrate_kernel<MODE, true, true> : rt_integrate_kernel<MODE, true, false>;
-  RT_CUDA(ctx, cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RT_CUDA(ctx, cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_prio));
   RT_CUDA(ctx, cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // below this many live rays a chain cannot fill the GPU with one thread per ray: switch to 3 lanes per ray
   const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
@@ -934,6 +939,10 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
           const long long before = C.upper;
           C.upper = *C.h;
           if (adapt) C.att = (C.upper * 100 >= before * 97) ? (C.att * 2 > 64 ? 64 : C.att * 2) : attempts;
+          // developer switch: a priority chain past its first `prio_keep` attempts keeps long slices while its rays die
+          // off (few blocks: their idle lanes cost little, every launch of theirs waits for SM slots)
+          static const long long prio_keep = dev_env("RT_PRIO_KEEP_ATT", 0);
+          if (adapt && prio_keep > 0 && (c & 1) && C.nominal >= prio_keep && C.att < 64) C.att = 64;
           if (dbg) {
             float ms = 0;
             cudaEventRecord(ctx->ev[2], C.st);
@@ -996,7 +1005,8 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           else
-            k1<<<grid_for(C.upper, RT_BLOCK), RT_BLOCK, smem, C.st>>>(
+            k1<<<grid_for(C.upper, RT_BLOCK), RT_BLOCK,
+                 ((c & 1) && ch[1].upper + ch[3].upper <= prio_smem_rays) ? smem_prio : smem, C.st>>>(
                 ctx->denv, O, S, C.idx[C.cur], C.cnt + (k % 3), C.idx[C.cur ^ 1], C.cnt + ((k + 1) % 3),
                 C.cnt + ((k + 2) % 3), att);
           C.cur ^= 1;
