@@ -52,6 +52,8 @@ PARTITION = "rotated"
 def partition_layout(world, is3d):
     """Rotated-strided; for the 3D sweeps on several GPUs the gather root gets a slightly smaller share (its step also
     holds the receive and placement of all ranks' records: ~0.2 ns per ray and rank against 53 ns of tracing per ray)."""
+    if LAYOUT_OVERRIDE:
+        return LAYOUT_OVERRIDE
     if world > 1 and is3d:
         return "rootlight:%d" % max(2, int(round(1.0 / (0.004 * world))))
     return PARTITION
@@ -68,6 +70,7 @@ def parse():
     ap.add_argument("--rays-per-gpu", type=int, default=0, help="override (testing only)")
     ap.add_argument("--slice", type=int, default=0)
     ap.add_argument("--coop-threshold", type=int, default=0, help="developer: rt_solver_opts.coop_threshold (0 = default)")
+    ap.add_argument("--layout", default="", help="developer: launch-list partition across ranks (default: see partition_layout)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="rays in the CPU sample (0 = default)")
     ap.add_argument("--maxiters", type=int, default=0, help="iteration cap override (a cut-off run: named in config)")
     ap.add_argument("--skip-e2e", action="store_true",
@@ -103,6 +106,7 @@ def make_launch(workload, world, rank, rays_per_gpu=0):
 
 MAXITERS_OVERRIDE = 0
 COOP_THRESHOLD = 0
+LAYOUT_OVERRIDE = ""
 
 
 def solver_kwargs(workload, slice_attempts=0):
@@ -238,8 +242,9 @@ def run_reference(args, rank, world):
 
 
 def main():
-    global MAXITERS_OVERRIDE, COOP_THRESHOLD
+    global MAXITERS_OVERRIDE, COOP_THRESHOLD, LAYOUT_OVERRIDE
     args = parse()
+    LAYOUT_OVERRIDE = args.layout
     MAXITERS_OVERRIDE = args.maxiters
     COOP_THRESHOLD = args.coop_threshold
     rank = int(os.environ.get("RANK", "0"))
@@ -319,6 +324,14 @@ def main():
     dev_res = {"u_end": u_end.cpu().numpy(), "t_end": t_end.cpu().numpy(), "group_delay": gd.cpu().numpy(),
                "status": status_h, "naccept": ints[1].cpu().numpy(), "nreject": ints[2].cpu().numpy(),
                "nfe": ints[3].cpu().numpy(), "nreflect": ints[4].cpu().numpy()}
+    # diagnostic, outside the timed region: what the gather costs its root (all ranks take part)
+    gather_ms = None
+    if world > 1:
+        gather_ms = {}
+        for _ in range(3):
+            barrier()
+            multi.gather_terminal(rec_d, ints, n_total, rank, world, layout=partition_layout(world, is3d), timing=gather_ms)
+
     # trajectory output (save workloads): rows written per step, the same sweep without saving, and the CSR packing
     traj = None
     if rank == 0 and solver_kwargs(args.workload).get("save_mode"):
@@ -466,6 +479,7 @@ def main():
                 "value": nfe_all * K / (e2e_all * 1e-3), "unit": "RHS evals/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_all / K, "rays_per_s": rays_all * K / (e2e_all * 1e-3)},
             "trajectory": traj,
+            "gather_root_ms": gather_ms,
             "gpu_launches": int(launches_all),
             "by_rank": by_rank,
             "clocks": clocks,

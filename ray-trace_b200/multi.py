@@ -49,10 +49,18 @@ class _Plan:
 
     def __init__(self, n_total, world, dst, layout, d, i):
         self.sizes, self.place = [], []
+        self.n_total, self.world = n_total, world
+        self.block = int(layout.split(":")[1]) if layout.startswith("blockcyclic:") else (4096 if layout == "blockcyclic" else 0)
+        self.full = n_total // (world * self.block) if self.block else 0  # complete cycles of `world` blocks
         for r in range(world):
             idx = _indices(n_total, r, world, layout)
             self.sizes.append(int(idx.size))
-            if layout == "contiguous":
+            if self.block:
+                # the complete cycles are a strided view of the assembled array (coalesced block copies); only the
+                # rays of the last, incomplete cycle are placed by index
+                tail = idx[self.full * self.block:]
+                self.place.append(torch.from_numpy(tail).to(d.device))
+            elif layout == "contiguous":
                 lo = int(idx[0]) if idx.size else 0
                 self.place.append(slice(lo, lo + int(idx.size)))
             elif layout == "strided":
@@ -66,6 +74,18 @@ class _Plan:
 
     def put(self, r, d, i):
         p = self.place[r]
+        if self.block:
+            nb = self.full * self.block
+            if nb:
+                cyc = self.full * self.world * self.block
+                for src, dst_ in ((d, self.D), (i, self.I)):
+                    rows = src.shape[0]
+                    dst_[:, :cyc].view(rows, self.full, self.world, self.block)[:, :, r, :] = \
+                        src[:, :nb].view(rows, self.full, self.block)
+            if p.numel():
+                self.D.index_copy_(1, p, d[:, nb:])
+                self.I.index_copy_(1, p, i[:, nb:])
+            return
         if isinstance(p, slice):
             self.D[:, p] = d
             self.I[:, p] = i
@@ -77,11 +97,12 @@ class _Plan:
 _PLANS = {}
 
 
-def gather_terminal(d, i, n_total, rank, world, dst=0, group=None, layout="contiguous"):
+def gather_terminal(d, i, n_total, rank, world, dst=0, group=None, layout="contiguous", timing=None):
     """Gather per-rank records (partitions of n_total rays, see sweeps.partition_indices / block_cyclic_indices;
     layout "contiguous" | "strided" | "rotated" | "blockcyclic[:B]") to rank `dst`, in launch-list order.
     Returns (doubles [rows, n_total], ints [5, n_total]) on dst — buffers owned by this module and overwritten by the
-    next call with the same shapes — and (None, None) elsewhere."""
+    next call with the same shapes — and (None, None) elsewhere.  timing (a dict, CUDA tensors only): on dst it receives
+    the milliseconds spent waiting for the receives and placing the records (diagnostics; synchronises the device)."""
     if world == 1:
         return d, i
     if rank != dst:
@@ -99,11 +120,21 @@ def gather_terminal(d, i, n_total, rank, world, dst=0, group=None, layout="conti
         if r != dst:
             ops.append(dist.P2POp(dist.irecv, plan.dbuf[r], r, group))
             ops.append(dist.P2POp(dist.irecv, plan.ibuf[r], r, group))
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if (timing is not None and d.is_cuda) else None
+    if ev:
+        ev[0].record()
     reqs = dist.batch_isend_irecv(ops)
     plan.put(dst, d, i)  # own records while the others are in flight
     for q in reqs:
         q.wait()
+    if ev:
+        ev[1].record()
     for r in range(world):
         if r != dst:
             plan.put(r, plan.dbuf[r], plan.ibuf[r])
+    if ev:
+        ev[2].record()
+        torch.cuda.synchronize()
+        timing["receive_ms"] = ev[0].elapsed_time(ev[1])
+        timing["place_ms"] = ev[1].elapsed_time(ev[2])
     return plan.D, plan.I

@@ -52,6 +52,8 @@ def partition_indices(n, rank, world, layout="contiguous"):
     Rays are independent, so any partition gives the same per-ray results; strided balances sweeps whose expensive
     rays cluster in one part of the launch list (cfg3: the long magnetospheric paths sit at high colatitude)."""
     import numpy as _np
+    if layout.startswith("blockcyclic"):  # "blockcyclic[:B]": blocks of B rays go round the ranks (block_cyclic_indices)
+        return block_cyclic_indices(n, int(layout.split(":")[1]) if ":" in layout else 4096, world, rank)
     if layout.startswith("rootlight"):
         # "rootlight:K" = rotated, except that in every K-th block of `world` rays the ray that would go to rank 0 goes
         # to one of the other ranks (round robin): the gather root traces 1/K fewer rays and spends the time it saves on

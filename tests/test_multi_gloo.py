@@ -49,7 +49,7 @@ def _worker(rank, world, port, out_path, n_total, layout):
 import pytest
 
 
-@pytest.mark.parametrize("layout", ["contiguous", "strided", "rotated", "blockcyclic:8", "rootlight:3"])
+@pytest.mark.parametrize("layout", ["contiguous", "strided", "rotated", "blockcyclic:8", "blockcyclic:64", "rootlight:3"])
 def test_two_rank_partition_and_gather(tmp_path, layout):
     from raytrace_b200 import sweeps
     n_total = 101  # odd: ragged partitions 50 + 51
