@@ -50,13 +50,13 @@ PARTITION = "rotated"
 
 
 def partition_layout(world, is3d):
-    """Rotated-strided; for the 3D sweeps on several GPUs the gather root gets a slightly smaller share (its step also
-    holds the receive and placement of all ranks' records: ~0.2 ns per ray and rank against 53 ns of tracing per ray)."""
+    """Across ranks: blocks of 4096 consecutive rays go round the ranks (as rt_solve_*_multi does inside the library).
+    Work per rank within 0.5 % on the 8 x 10^6-ray sweep, and the root places every rank's records with block copies:
+    measured on 8 GPUs 55.2 ms per step (gather: 1.0 ms receive + 0.4 ms placement) against 56.0 ms with the per-ray
+    rotated layout (1.2 ms of indexed placement) — profiles/r2_bench_cfg3_8gpu_layout_*.json."""
     if LAYOUT_OVERRIDE:
         return LAYOUT_OVERRIDE
-    if world > 1 and is3d:
-        return "rootlight:%d" % max(2, int(round(1.0 / (0.004 * world))))
-    return PARTITION
+    return "blockcyclic:4096" if world > 1 else PARTITION
 NCU_DRAM_BYTES_PER_FULL_LAUNCH = {"cfg3": 296.8e6, "cfg5": None, "cfg2": 13.3e6, "cfg4": None, "cfg2save": None}
 
 
