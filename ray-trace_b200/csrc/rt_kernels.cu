@@ -920,8 +920,9 @@ static int run_solve(rt_ctx *ctx, long long n, const RtLaunch &L, const rt_resul
   const long long early_min = dev_env("RT_EARLY_MIN", 262144);
   const bool early = ctx->early_host != nullptr && n >= early_min;
   // (late rays are patched in by a host scatter of 14 cache lines each, 0.13 us per ray: the snapshot waits until
-  // n / 512 rays are left — 2 ms before the end of cfg3, enough for its 92 MB)
-  static const long long early_div = dev_env("RT_EARLY_DIV", 512);
+  // n / 128 rays are left — on cfg3 that is ~4 ms before the end, enough for its 92 MB; measured e2e 56.5 ms with
+  // n / 512 or no early copy at all, 55.5 ms with n / 128, 56.0 with n / 32: profiles/r2_early_copy_matrix.log)
+  static const long long early_div = dev_env("RT_EARLY_DIV", 128);
   const long long early_thr = (n / early_div < 1024) ? 1024 : ((n / early_div > RT_LATE_CAP) ? RT_LATE_CAP : n / early_div);
   bool early_trigger = false, snap[4] = {false, false, false, false};
   int nsnap = 0;
