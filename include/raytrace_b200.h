@@ -178,6 +178,26 @@ RT_API int rt_solve_3d_device(rt_ctx *ctx, int64_t n, const double *r, const dou
                               const double *rho_phi, const double *T0, const double *f,
                               const double *t0, rt_result *res);
 
+/* rt_solve_3d_device_static: rt_solve_3d_device for callers that cannot allocate device memory.
+ * No counterpart in the reference: added for callers that may
+ * not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments (every pointer in DEVICE memory), same results bit for bit, but the integrator's
+ * working set (FSAL derivative, step sizes, work lists, counters: 100 bytes per ray) lives in a
+ * file-scope device array of the library instead of cudaMalloc'ed buffers, and the call itself makes
+ * no cudaMalloc / cudaFree / allocating library call.  Limits: n <= RT_STATIC_MAX_RAYS (larger n is
+ * refused with RT_ERR_INVALID and a message naming the limit); save_mode must be 0 (trajectory rows
+ * need the growable buffer of the allocating entry points: RT_ERR_STATE).  Every device that loads the
+ * library holds the array (RT_STATIC_SCRATCH_BYTES, ~1.6 MB) until the process exits.  ALL contexts of
+ * a device share it and it keeps the previous call's contents (the call clears the counters it needs
+ * at zero): two such calls that overlap on one GPU — two contexts, two host threads — race; serialise
+ * them.  The call runs one chain of slices on the context's stream and returns after it drained. */
+#define RT_STATIC_MAX_RAYS 16384
+#define RT_STATIC_SCRATCH_BYTES (256 + 100 * RT_STATIC_MAX_RAYS)
+RT_API int rt_solve_3d_device_static(rt_ctx *ctx, int64_t n, const double *r, const double *theta,
+                                     const double *phi, const double *rho_r, const double *rho_theta,
+                                     const double *rho_phi, const double *T0, const double *f,
+                                     const double *t0, rt_result *res);
+
 /* counters and timings of the last solve of a context (rt_get_stats, rt_multi_get_stats) */
 typedef struct rt_stats {
   int64_t kernel_launches;   /* kernels launched by the last solve */

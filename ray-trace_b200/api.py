@@ -543,3 +543,17 @@ def _solve_device(self, n, col_ptrs, res_ptrs):
 
 
 RayTracer.solve_device = _solve_device
+
+
+def _solve_device_static(self, n, col_ptrs, res_ptrs):
+    """rt_solve_3d_device_static: solve_device without device allocations (the integrator's working set lives in a
+    static device array of the library); 3D only, n <= STATIC_MAX_RAYS, save_mode 0.  Not in the reference: added for
+    callers that may not call cudaMalloc (include/raytrace_b200.h)."""
+    cres = _Result(*[C.c_void_p(res_ptrs[k]) for k, _ in _Result._fields_])
+    _check(self._L.rt_solve_3d_device_static(self._ctx, C.c_int64(n), *[C.c_void_p(p) for p in col_ptrs], C.byref(cres)),
+           self._ctx, self._L)
+    return self.stats()
+
+
+STATIC_MAX_RAYS = 16384  # RT_STATIC_MAX_RAYS
+RayTracer.solve_device_static = _solve_device_static

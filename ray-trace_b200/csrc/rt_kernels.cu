@@ -118,6 +118,7 @@ struct rt_ctx {
   int last_mode = -1, last_max_samples = 0;
   rt_stats stats{};
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  unsigned char *static_scratch = nullptr;  // this device's address of rt_static_scratch (rt_solve_3d_device_static)
 };
 
 static int set_err(rt_ctx *ctx, int code, const char *fmt, ...) {
@@ -1182,6 +1183,145 @@ extern "C" int rt_solve_3d_device(rt_ctx *ctx, int64_t n, const double *r, const
                                   const double *T0, const double *f, const double *t0, rt_result *res) {
   const double *cols[9] = {r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0};
   return solve_common(ctx, n, cols, 9, res, true, true);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// The solve without allocations (rt_solve_3d_device_static; no counterpart in the reference, see the header): the
+// working set that ensure_work() cudaMallocs lives in this file-scope device array instead.  Layout for
+// N = RT_STATIC_MAX_RAYS (every part starts on a 256-byte boundary):
+//   [0, 64)        work-list counters (3 rotate, see run_solve), cleared by every call
+//   256            k1[7][n] FSAL derivative (56 N bytes reserved)
+//   256 + 56 N     h[N], qold[N], par[N]
+//   256 + 80 N     sgn[N], nsamp[N], trunc[N], work lists idx0[N], idx1[N]           total 256 + 100 N
+// Everything but the counters is written by rt_init_kernel before it is read, so stale contents of an earlier call are
+// harmless.  The array is per DEVICE and shared by all contexts of that device: overlapping calls race (header).
+// ---------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char rt_static_scratch[RT_STATIC_SCRATCH_BYTES];
+
+// Set-up, once per context, with the context's device current.  In host code the array's name is only a stand-in for
+// the symbol (not a device address): kernels get the address cudaGetSymbolAddress returns for the current device.
+static int static_scratch_ready(rt_ctx *ctx) {
+  if (ctx->static_scratch) return RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  void *p = nullptr;
+  const cudaError_t e = cudaGetSymbolAddress(&p, rt_static_scratch);
+  if (e != cudaSuccess || p == nullptr)
+    return set_err(ctx, RT_ERR_CUDA, "rt_solve_3d_device_static: cudaGetSymbolAddress(rt_static_scratch) on device %d: %s",
+                   ctx->device, cudaGetErrorString(e));
+  ctx->static_scratch = (unsigned char *)p;
+  return RT_OK;
+}
+
+extern "C" int rt_solve_3d_device_static(rt_ctx *ctx, int64_t n, const double *r, const double *theta, const double *phi,
+                                         const double *rho_r, const double *rho_theta, const double *rho_phi,
+                                         const double *T0, const double *f, const double *t0, rt_result *res) {
+  constexpr int MODE = RT_PRESET_RAY3D, DIM = RtTraits<MODE>::DIM;
+  static_assert(RT_STATIC_SCRATCH_BYTES == 256 + (size_t)RT_STATIC_MAX_RAYS * (DIM * 8 + 3 * 8 + 5 * 4), "scratch layout");
+  static_assert(RT_STATIC_MAX_RAYS % 64 == 0, "256-byte alignment of the parts");
+  if (!ctx) return set_err(ctx, RT_ERR_INVALID, "rt_solve_3d_device_static: null context");
+  if (n < 0) return set_err(ctx, RT_ERR_INVALID, "rt_solve_3d_device_static: n out of range");
+  if (n > RT_STATIC_MAX_RAYS)
+    return set_err(ctx, RT_ERR_INVALID,
+                   "rt_solve_3d_device_static: n = %lld exceeds RT_STATIC_MAX_RAYS = %d, the capacity of the static "
+                   "scratch array (use rt_solve_3d_device, which allocates, or split the launch list)",
+                   (long long)n, (int)RT_STATIC_MAX_RAYS);
+  if (ctx->env.preset != RT_PRESET_RAY3D)
+    return set_err(ctx, RT_ERR_INVALID, "rt_solve: environment preset %d does not match the 3D call", ctx->env.preset);
+  const RtDevOpts O = make_dev_opts(ctx->opts);
+  if (O.save_mode)
+    return set_err(ctx, RT_ERR_STATE, "rt_solve_3d_device_static: save_mode must be 0 (trajectory rows need the growable "
+                                      "buffer of rt_solve_3d_device)");
+  if (n == 0) {
+    ctx->last_n = 0;
+    ctx->stats = rt_stats{};
+    return RT_OK;
+  }
+  if (!result_ok(res)) return set_err(ctx, RT_ERR_INVALID, "rt_solve: rt_result has null members");
+  const double *cols[9] = {r, theta, phi, rho_r, rho_theta, rho_phi, T0, f, t0};
+  RtLaunch L{};
+  for (int k = 0; k < 9; k++) {
+    if (!cols[k]) return set_err(ctx, RT_ERR_INVALID, "rt_solve: launch-list column %d is null", k);
+    L.col[k] = cols[k];
+  }
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (int rc = static_scratch_ready(ctx)) return rc;
+  const rt_result &R = *res;
+  constexpr size_t N = RT_STATIC_MAX_RAYS;
+  int *cnt = (int *)ctx->static_scratch;
+  RtState S;
+  S.n = n;
+  S.u = R.u_end;
+  S.k1 = (double *)(ctx->static_scratch + 256);
+  S.t = R.t_end;
+  S.h = S.k1 + DIM * N;
+  S.qold = S.h + N;
+  S.par = S.qold + N;
+  S.status = R.status;
+  S.naccept = R.naccept;
+  S.nreject = R.nreject;
+  S.nfe = R.nfe;
+  S.nreflect = R.nreflect;
+  S.sgn = (int *)(S.par + N);
+  S.nsamp = S.sgn + N;
+  S.trunc = S.nsamp + N;
+  S.traj = nullptr;
+  int *idx[2] = {S.trunc + N, S.trunc + 2 * N};
+  cudaStream_t st = ctx->stream;
+  const size_t smem = (size_t)(7 * DIM) * RT_BLOCK * sizeof(double);
+  auto k1 = rt_integrate_kernel<MODE, false, false>;
+  auto k3 = rt_integrate_kernel<MODE, true, false>;
+  RT_CUDA(ctx, cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RT_CUDA(ctx, cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const long long coop_threshold = ctx->opts.coop_threshold == 0 ? 10000 : ctx->opts.coop_threshold;
+  const int attempts = ctx->opts.slice_attempts > 0 ? ctx->opts.slice_attempts : 4;
+  const bool adapt = ctx->opts.slice_attempts <= 0;
+  ctx->stats = rt_stats{};
+  ctx->last_mode = -1;  // no trajectories to fetch after this call
+  ctx->last_max_samples = 0;
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
+  RT_CUDA(ctx, cudaMemsetAsync(cnt, 0, 16 * sizeof(int), st));  // the array keeps the previous call's counters
+  rt_init_kernel<MODE><<<grid_for(n, RT_BLOCK), RT_BLOCK, 0, st>>>(ctx->denv, O, S, L, idx[0], cnt, nullptr, cnt + 4);
+  RT_CUDA(ctx, cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
+  // one chain of slices (run_solve's rotation of three counters); n bounds the list until the first count is read
+  long long upper = n;
+  int cur = 0, k = 0, att = attempts;
+  while (upper > 0) {
+    const bool coop = upper <= coop_threshold;  // 3 lanes per ray once the list cannot fill the GPU
+    const int a = coop ? (att > 32 ? att : 32) : att;
+    const int batch = coop ? 4 : 8;
+    for (int b = 0; b < batch; b++, k++) {
+      if (coop)
+        k3<<<grid_for(upper, (RT_BLOCK / 32) * RT_COOP_RAYS_PER_WARP), RT_BLOCK, smem, st>>>(
+            ctx->denv, O, S, idx[cur], cnt + (k % 3), idx[cur ^ 1], cnt + ((k + 1) % 3), cnt + ((k + 2) % 3), a);
+      else
+        k1<<<grid_for(upper, RT_BLOCK), RT_BLOCK, smem, st>>>(ctx->denv, O, S, idx[cur], cnt + (k % 3), idx[cur ^ 1],
+                                                             cnt + ((k + 1) % 3), cnt + ((k + 2) % 3), a);
+      cur ^= 1;
+      ctx->stats.kernel_launches++;
+      ctx->stats.slices++;
+    }
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->h_count, cnt + (k % 3), sizeof(int), cudaMemcpyDeviceToHost, st));  // pinned (rt_create)
+    RT_CUDA(ctx, cudaStreamSynchronize(st));
+    const long long before = upper;
+    upper = ctx->h_count[0];
+    if (adapt) att = (upper * 100 >= before * 97) ? (att * 2 > 64 ? 64 : att * 2) : attempts;
+  }
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
+  rt_group_delay_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, R.u_end + (size_t)(DIM - 1) * n, S.par, 1, R.group_delay);
+  RT_CUDA(ctx, cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  RT_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
+  RT_CUDA(ctx, cudaStreamSynchronize(st));
+  float ms_int = 0, ms_tot = 0;
+  RT_CUDA(ctx, cudaEventElapsedTime(&ms_int, ctx->ev[1], ctx->ev[2]));
+  RT_CUDA(ctx, cudaEventElapsedTime(&ms_tot, ctx->ev[0], ctx->ev[3]));
+  ctx->stats.integrate_ms = ms_int;
+  ctx->stats.total_ms = ms_tot;
+  ctx->last_n = n;
+  return RT_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -89,6 +89,7 @@ def test_reference_facing_surface_is_bound():
     bound = {c[0] for c in julia_ccalls()}
     not_needed_from_julia = {
         "rt_solve_2d_device", "rt_solve_3d_device", "rt_set_stream", "rt_traj_pack_device",  # device-pointer callers
+            "rt_solve_3d_device_static",                                                           # same, without cudaMalloc
         "rt_measure_fp64_peak", "rt_multi_ctx",                                                 # bench / per-device access
         "rt_selftest_fastmath", "rt_debug_fallback_counts", "rt_debug_rhs3d", "rt_debug_fallback_samples",
         "rt_probe_latency",                                                                      # diagnostics
