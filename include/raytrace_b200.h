@@ -204,7 +204,7 @@ typedef struct rt_stats {
   int64_t slices;            /* integrate-kernel launches of the last solve */
   double integrate_ms;       /* CUDA-event time of the integrate kernels of the last solve */
   double total_ms;           /* CUDA-event time of the whole last solve on the stream */
-  int64_t total_nfe;         /* sum of nfe over rays of the last solve */
+  int64_t total_nfe;         /* reserved, always 0: the evaluation counts are per ray, rt_result.nfe */
   int64_t prio_rays;         /* rays the last solve put on the priority chain */
 } rt_stats;
 
