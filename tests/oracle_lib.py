@@ -190,7 +190,8 @@ def interior_events(reset=False):
     return int(lib().orc_interior_events(C.c_int(int(reset))))
 
 
-MATH = {"exp": 0, "exp10": 1, "log": 2, "log10": 3, "sin": 4, "cos": 5, "tan": 6, "atan": 7, "acos": 8, "pow_m4p5": 9}
+MATH = {"exp": 0, "exp10": 1, "log": 2, "log10": 3, "sin": 4, "cos": 5, "tan": 6, "atan": 7, "acos": 8, "pow_m4p5": 9,
+        "pow_b1": 10, "pow_b2": 11}
 
 
 def meridian_maps(E, x, y):

@@ -22,11 +22,21 @@ CASES = [
     ("sin", lambda: RNG.uniform(-1e6, 1e6, N), mp.sin, 1.0),
     ("cos", lambda: RNG.uniform(-1e12, 1e12, N), mp.cos, 1.0),
     ("tan", lambda: RNG.uniform(-1.5, 1.5, N), mp.tan, 2.0),
+    ("tan", lambda: RNG.uniform(-1e6, 1e6, N), mp.tan, 2.0),
+    # next to the poles, where tan = sin / cos divides by a cancelled cosine (the reduction's tail keeps it accurate)
+    ("tan", lambda: (RNG.integers(-1000, 1000, N) + 0.5) * np.pi + RNG.uniform(-1e-6, 1e-6, N), mp.tan, 2.5),
     ("atan", lambda: RNG.uniform(-5, 5, N), mp.atan, 1.0),
     ("atan", lambda: np.exp(RNG.uniform(-30, 30, N)), mp.atan, 1.0),
     ("acos", lambda: RNG.uniform(-1, 1, N), mp.acos, 1.0),
     ("acos", lambda: 1 - np.exp(RNG.uniform(-30, 0, N)), mp.acos, 1.0),
     ("pow_m4p5", lambda: RNG.uniform(1.0, 12.0, N), lambda v: v ** mp.mpf(-4.5), 4.0),
+    # the step controller's EEst^0.14 and qold^0.08 (rt_pow_pos = exp(p log x)): the documented bound is
+    # 1 + |p log x| ulp; error estimates between e^-12 and e^6 are what a solve at reltol 1e-3 .. 1e-9 produces,
+    # e^-60 .. e^30 is far outside (the factor is clamped to [1/5, 10] there anyway)
+    ("pow_b1", lambda: np.exp(RNG.uniform(-12, 6, N)), lambda v: mp.power(v, mp.mpf(0.14)), 1.0 + 0.14 * 12),
+    ("pow_b2", lambda: np.exp(RNG.uniform(-12, 6, N)), lambda v: mp.power(v, mp.mpf(0.08)), 1.0 + 0.08 * 12),
+    ("pow_b1", lambda: np.exp(RNG.uniform(-60, 30, N)), lambda v: mp.power(v, mp.mpf(0.14)), 1.0 + 0.14 * 60),
+    ("pow_b2", lambda: np.exp(RNG.uniform(-60, 30, N)), lambda v: mp.power(v, mp.mpf(0.08)), 1.0 + 0.08 * 60),
 ]
 
 
